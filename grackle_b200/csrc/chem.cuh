@@ -1,0 +1,252 @@
+// grackle-b200: the per-cell cooling/heating rate and the chemistry network update.
+// (continuation of physics.cuh; same conventions)
+#ifndef GRB200_CHEM_CUH
+#define GRB200_CHEM_CUH
+
+#include "physics.cuh"
+
+namespace grb {
+
+// One cell, proper (not comoving) densities, all in registers.
+struct Cell {
+  double d, e, de, HI, HII, HeI, HeII, HeIII, HM, H2I, H2II, DI, DII, HDI, metal, dust;
+  // optional per-cell source terms (0 when the physics is off)
+  double vheat, mheat, kphHI, kphHeI, kphHeII, kdissH2I, photogamma, xH2shield, isrf, fshield;
+};
+
+// what cool_rate leaves behind for the rest of the subcycle (the reference's row temporaries)
+struct Thermo {
+  double edot, tgas, mmw, p2d, tdust, metallicity, dust2gas, rhoH, myde;
+};
+
+// two adjacent rows of a packed table -> lerp of column `col`
+// cooling tables: a + t*(b-a) (cool1d_multi_g.F:387-410); rate tables: a + (b-a)*t
+// (solve_rate_cool_g.F:1225-1240).  Both spellings round identically.
+__device__ __forceinline__ double lerp_row(const double *row, int ncol, int col, double t)
+{
+  const double a = ld(row + col), b = ld(row + ncol + col);
+  return a + (b - a) * t;
+}
+
+// Rahmati+13 eq. 13/14 shielding fraction (cool1d_multi_g.F:788-792, solve_rate_cool_g.F:1518-1520)
+__device__ __forceinline__ double rahmati_f(double nratio)
+{
+  return 0.98 * pow(1.0 + pow(nratio, 1.64), -2.28) + 0.02 * pow(1.0 + nratio, -0.84);
+}
+
+struct TIndex { int idx; double t1, t2, tdef; };   // idx is 1-based like the Fortran
+
+__device__ __forceinline__ TIndex t_index(const GrParams &P, double logtem)
+{
+  TIndex r;
+  r.idx = (int)imin(P.nratec - 1, imax(1, (long long)((logtem - P.logtem0) / P.dlogtem) + 1));
+  r.t1 = (P.logtem0 + (r.idx - 1) * P.dlogtem);
+  r.t2 = (P.logtem0 + (r.idx) * P.dlogtem);
+  r.tdef = (logtem - r.t1) / (r.t2 - r.t1);
+  return r;
+}
+
+// ---------------------------------------------------------------------------------
+// cool1d_multi_g (cool1d_multi_g.F:6-1131) for one cell.  `first` = (iter == 1).
+// tgasold is the per-cell carry between subcycles.
+// ---------------------------------------------------------------------------------
+template <int PC>
+__device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, double &tgasold,
+                                 Thermo &th)
+{
+  const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
+  const double dom = P.dom, dom_inv = P.dom_inv;
+  double edot = 0.0;
+  th.p2d = (P.gamma - 1.0) * c.d * c.e;
+  th.tdust = 0.0; th.metallicity = 0.0; th.dust2gas = 0.0;
+
+  if (PC == 0) {
+    th.rhoH = (P.imetal == 1) ? P.fh * (c.d - c.metal) : P.fh * c.d;
+    temperature_table(P, c.d, c.e, c.metal, th.rhoH, th.tgas, th.mmw);
+    th.myde = 0.0;
+  } else {
+    double mmw = (c.HeI + c.HeII + c.HeIII) / 4.0 + c.HI + c.HII + c.de;
+    th.rhoH = c.HI + c.HII;
+    th.myde = c.de;
+    if (PC > 1) {
+      mmw = mmw + c.HM + (c.H2I + c.H2II) / 2.0;
+      th.rhoH = th.rhoH + c.H2I + c.H2II;
+    }
+    if (P.imetal == 1) mmw = mmw + c.metal / GRB_MU_METAL;
+    th.tgas = dmax(th.p2d * P.utem / mmw, P.temstart);
+    th.mmw = c.d / mmw;
+    if (PC > 1) {    // H2 vibrational gamma correction (:294-318)
+      const double nH2 = 0.5 * (c.H2I + c.H2II);
+      const double nother = (c.HeI + c.HeII + c.HeIII) / 4.0 + c.HI + c.HII + c.de;
+      double gamma2;
+      if (nH2 / nother > 1.0e-3) {
+        const double x = 6100.0 / th.tgas;
+        if (x > 10.0) {
+          gamma2 = 0.5 * 5.0;
+        } else {
+          const double ex = exp(x);
+          gamma2 = 0.5 * (5.0 + 2.0 * (x * x) * ex / ((ex - 1) * (ex - 1)));
+        }
+      } else {
+        gamma2 = 2.5;
+      }
+      gamma2 = 1.0 + (nH2 + nother) / (nH2 * gamma2 + nother / (P.gamma - 1.0));
+      th.tgas = th.tgas * (gamma2 - 1.0) / (P.gamma - 1.0);
+    }
+  }
+
+  if (P.imetal == 1) th.metallicity = c.metal / c.d / P.z_solar;
+  const double mynh = th.rhoH * dom;
+  if (first) tgasold = th.tgas;
+
+  double logtem = log(0.5 * (th.tgas + tgasold));
+  logtem = dmax(logtem, P.logtem0);
+  logtem = dmin(logtem, P.logtem9);
+
+  const bool interp = (PC > 0) || (P.idustall > 0);
+  const double *row = P.cool;
+  double tdef = 0.0;
+  if (interp) {
+    const TIndex ti = t_index(P, logtem);
+    row = P.cool + (size_t)(ti.idx - 1) * NCOOL;
+    tdef = ti.tdef;
+  }
+#define COOL_LERP(col) lerp_row(row, NCOOL, col, tdef)
+
+  if (PC > 0) {     // six-species atomic cooling (:417-446)
+    const double ceHI = COOL_LERP(L_CEHI), ceHeI = COOL_LERP(L_CEHEI), ceHeII = COOL_LERP(L_CEHEII);
+    const double ciHI = COOL_LERP(L_CIHI), ciHeI = COOL_LERP(L_CIHEI), ciHeIS = COOL_LERP(L_CIHEIS);
+    const double ciHeII = COOL_LERP(L_CIHEII), reHII = COOL_LERP(L_REHII);
+    const double reHeII1 = COOL_LERP(L_REHEII1), reHeII2 = COOL_LERP(L_REHEII2);
+    const double reHeIII = COOL_LERP(L_REHEIII), brem = COOL_LERP(L_BREM);
+    const double de = c.de;
+    edot = (- ceHI * c.HI * de
+            - ceHeI * c.HeII * (de * de) * dom / 4.0
+            - ceHeII * c.HeII * de / 4.0
+            - ciHI * c.HI * de
+            - ciHeI * c.HeI * de / 4.0
+            - ciHeII * c.HeII * de / 4.0
+            - ciHeIS * c.HeII * (de * de) * dom / 4.0
+            - reHII * c.HII * de
+            - reHeII1 * c.HeII * de / 4.0
+            - reHeII2 * c.HeII * de / 4.0
+            - reHeIII * c.HeIII * de / 4.0
+            - brem * (c.HII + c.HeII / 4.0 + c.HeIII) * de);
+  }
+
+  if (PC > 1) {     // H2 cooling, Glover & Abel (2008) (:472-526), CIE (:630-649)
+    const double gaHI = COOL_LERP(L_GAHI), gaH2 = COOL_LERP(L_GAH2), gaHe = COOL_LERP(L_GAHE);
+    const double gaHp = COOL_LERP(L_GAHP), gael = COOL_LERP(L_GAEL), h2lte = COOL_LERP(L_H2LTE);
+    double fudge = 1.0;
+    if (P.ih2optical == 1) {
+      fudge = pow(0.76 * c.d * dom / 8.e9, -0.45);
+      fudge = dmin(fudge, 1.0);
+    }
+    const double galdl = gaHI * c.HI + gaH2 * c.H2I / 2.0 + gaHe * c.HeI / 4.0 + gaHp * c.HII + gael * c.de;
+    const double gphdl1 = h2lte / dom;
+    edot = edot - (double)P.ih2co * fudge * c.H2I * h2lte / (1.0 + gphdl1 / galdl) / (2.0 * dom);
+    if (P.iciecool == 1 && c.d * dom > 1e10) {
+      const double cieco = COOL_LERP(L_CIECO);
+      double tau = pow((c.d / 2e16) * dom, 2.8);
+      tau = dmax(tau, 1.e-5);
+      double ciefudge = dmin((1.0 - exp(-tau)) / tau, 1.0);
+      tau = pow((c.d / 2.e18) * dom, 8.0);
+      tau = dmax(tau, 1.e-5);
+      ciefudge = ciefudge * dmin((1.0 - exp(-tau)) / tau, 1.0);
+      edot = ciefudge * (edot - c.H2I * (c.d * cieco));
+    }
+  }
+
+  if (PC > 2) {     // HD cooling (:655-686)
+    double hdlte, hdlow;
+    if (th.tgas > P.comp2) { hdlte = COOL_LERP(L_HDLTE); hdlow = COOL_LERP(L_HDLOW); }
+    else { hdlte = GRB_TINY; hdlow = GRB_TINY; }
+    const double hdlte1 = hdlte / (c.HI * dom);
+    const double hdlow1 = dmax(hdlow, GRB_TINY);
+    edot = edot - c.HDI * (hdlte / (1.0 + hdlte1 / hdlow1)) / (3.0 * dom);
+  }
+
+  if (anydust || (P.igammah > 0))
+    th.dust2gas = (P.idustfield > 0) ? c.dust / c.d : P.fgr * th.metallicity;
+  double myisrf = 0.0;
+  if (anydust || (P.igammah > 1)) myisrf = (P.iisrffield > 0) ? c.isrf : P.isrf;
+
+  if (anydust) {    // gas-grain heat transfer and T_dust (:726-753)
+    const double gasgr = COOL_LERP(L_GASGR);
+    const double gasgr_tdust = P.fgr * gasgr * P.coolunit / GRB_MASS_H;
+    th.tdust = dust_temperature(th.tgas, mynh, gasgr_tdust, P.gamma_isrfa, myisrf, P.comp2);
+    edot = edot - gasgr * (th.tgas - th.tdust) * th.dust2gas * th.rhoH * th.rhoH;
+  }
+
+  if (PC > 0) {     // UVB photo-heating with optional self-shielding (:758-913)
+    double fH = 1.0, fHe = 1.0;
+    if (P.iradshield >= 1 && !(P.k24 < GRB_TINY8)) {
+      const double nSSh = P.ssh_sig_hi * pow(th.tgas / 1.0e4, 0.17) * P.ssh_k24;
+      fH = rahmati_f((c.HI + c.HII) * dom / nSSh);
+    }
+    if (P.iradshield >= 2 && !(P.k26 < GRB_TINY8)) {
+      const double nSSh_he = P.ssh_sig_hei * pow(th.tgas / 1.0e4, 0.17) * P.ssh_k26;
+      fHe = rahmati_f(0.25 * (c.HeI + c.HeII + c.HeIII) * dom / nSSh_he);
+    }
+    const double ip = (double)P.ipiht;
+    if (P.iradshield == 0)
+      edot = edot + ip * (P.piHI * c.HI + P.piHeI * c.HeI * 0.25 + P.piHeII * c.HeII * 0.25) / dom;
+    else if (P.iradshield == 1)
+      edot = edot + ip * (P.piHI * c.HI * fH + P.piHeI * c.HeI * 0.25 + P.piHeII * c.HeII * 0.25) / dom;
+    else if (P.iradshield == 2)
+      edot = edot + ip * (P.piHI * c.HI * fH + P.piHeI * c.HeI * 0.25 * fHe + P.piHeII * c.HeII * 0.25) / dom;
+    else if (P.iradshield == 3)
+      edot = edot + ip * (P.piHI * c.HI * fH + P.piHeI * c.HeI * fHe) / dom;
+  }
+
+  if (PC == 0) {    // Cloudy primordial cooling + electron density from mu (:917-947)
+    edot = edot + cloudy_edot(P, P.pri, th.rhoH, th.metallicity, logtem, 0, 0);
+    double myde = 1 - th.mmw * (3.0 * P.fh + 1.0) / 4.0;
+    if (P.imetal == 1) myde = myde - th.mmw * c.metal / (c.d * GRB_MU_METAL);
+    myde = c.d * myde / th.mmw;
+    th.myde = dmax(myde, 0.0);
+  }
+
+  if (P.igammah > 0) {   // photo-electric heating by dust (:951-1001)
+    double geff;
+    if (P.igammah == 1) {
+      geff = (th.tgas > 2.e4) ? 0.0 : P.gammaha;
+    } else if (P.igammah == 2) {
+      geff = (th.tgas > 2.e4) ? 0.0 : P.gammaha * 0.05 * myisrf;
+    } else {
+      const double pe_X = myisrf * dom_inv * sqrt(th.tgas) / th.myde;
+      const double pe_eps = (4.9e-2 / (1.0 + pow(pe_X / 1925.0, 0.73))) +
+                            ((3.7e-2 * pow(th.tgas / 1.e4, 0.7)) / (1.0 + (pe_X / 5000.0)));
+      geff = P.gammaha * pe_eps * myisrf;
+    }
+    edot = edot + geff * th.rhoH * dom_inv * th.dust2gas / P.fgr;
+  }
+
+  if ((P.idustall > 0) || (P.idustrec > 0)) {   // grain recombination cooling (:1005-1023)
+    const double regr = COOL_LERP(L_REGR);
+    const double grbeta = 0.74 / pow(th.tgas, 0.068);
+    edot = edot - regr * pow(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
+  }
+
+  // Compton + X-ray Compton (:1027-1041)
+  edot = edot - P.comp1 * (th.tgas - P.comp2) * th.myde * dom_inv -
+         P.comp_xraya * (th.tgas - P.comp_temp) * th.myde * dom_inv;
+
+  if (P.iradtrans == 1)
+    edot = edot + (double)P.ipiht * c.photogamma / P.coolunit * c.HI / dom;
+
+  if (P.imcool == 1) {   // Cloudy metal cooling (:1069-1097)
+    if (P.clnew == 1) edot = edot + cloudy_edot(P, P.met, th.rhoH, th.metallicity, logtem, P.icmbTfloor, 1);
+    else edot = edot + cloudy_old_edot(P, P.met, c.d, th.rhoH, th.metallicity, logtem);
+  }
+
+  if (P.iVheat == 1) edot = edot + c.vheat / P.coolunit / (dom * dom);
+  if (P.iMheat == 1) edot = edot + c.mheat * c.d * GRB_MASS_H / P.coolunit / dom;
+#undef COOL_LERP
+
+  tgasold = th.tgas;
+  th.edot = edot;
+}
+
+}  // namespace grb
+#endif

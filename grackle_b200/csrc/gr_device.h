@@ -1,0 +1,104 @@
+// grackle-b200: data layout shared by the host launcher and the sm_100a kernels.
+//
+// HBM layout
+// ----------
+//  * Fields: the caller's SoA arrays, untouched layout (i fastest).  One thread owns
+//    one active cell; a warp reads 32 consecutive i => 256-byte coalesced segments.
+//  * Per-T tables: re-packed from the reference's 70 separate 600-entry arrays
+//    (chemistry_data_storage) into two row-major matrices
+//        chem[bin][NCHEM]   (k1..k58, ncr*, k13dd*14)      600 x 46 doubles = 221 KB
+//        cool[bin][NCOOL]   (ceHI..brem, GA*, H2LTE, ...)  600 x 24 doubles = 115 KB
+//    so the two bins a cell interpolates between are ONE contiguous span
+//    (2 x 368 B resp. 2 x 192 B) instead of 92 scattered 8-byte gathers.
+//  * h2dust[dustbin][bin] (1.2 MB) and the Cloudy grids stay in the reference's
+//    order (T fastest) and are read through the read-only path (L2-resident).
+#ifndef GRB200_DEVICE_H
+#define GRB200_DEVICE_H
+
+#include <cstdint>
+
+// column indices of the packed chemistry-rate matrix
+enum {
+  C_K1 = 0, C_K2, C_K3, C_K4, C_K5, C_K6, C_K57, C_K58,          // 6-species network
+  C_K7, C_K8, C_K9, C_K10, C_K11, C_K12, C_K13, C_K14, C_K15,    // + H2
+  C_K16, C_K17, C_K18, C_K19, C_K22, C_NCRN, C_NCRD1, C_NCRD2,
+  C_K13DD0,                                                       // 14 columns
+  C_K50 = C_K13DD0 + 14, C_K51, C_K52, C_K53, C_K54, C_K55, C_K56,  // + D
+  NCHEM
+};
+static_assert(NCHEM == 46, "packed chemistry row is 46 doubles");
+
+// column indices of the packed cooling-rate matrix
+enum {
+  L_CEHI = 0, L_CEHEI, L_CEHEII, L_CIHI, L_CIHEI, L_CIHEIS, L_CIHEII,
+  L_REHII, L_REHEII1, L_REHEII2, L_REHEIII, L_BREM,
+  L_GAHI, L_GAH2, L_GAHE, L_GAHP, L_GAEL, L_H2LTE, L_CIECO,
+  L_HDLTE, L_HDLOW, L_GASGR, L_REGR, L_PAD,
+  NCOOL
+};
+static_assert(NCOOL == 24, "packed cooling row is 24 doubles");
+
+struct GrCloudyDev {
+  long long rank;
+  long long dim[5];
+  const double *par[5];
+  const double *cooling;
+  const double *heating;
+  const double *mmw;
+  // cell-invariant pieces hoisted to the host (cool1d_cloudy_g.F:107-153)
+  double dpar[5];          // uniform-grid spacing per axis
+  long long zindex;        // 1-based index into the redshift axis
+  int end_int;             // redshift beyond the table: use the last z-plane (2Df3D)
+  int get_heat;            // heating table applies at this redshift
+};
+
+// the 15 density-like fields + energy, in the order the kernels index them
+enum {
+  F_D = 0, F_E, F_DE, F_HI, F_HII, F_HEI, F_HEII, F_HEIII, F_HM, F_H2I, F_H2II,
+  F_DI, F_DII, F_HDI, F_METAL, F_DUST,
+  F_VHEAT, F_MHEAT, F_KPHHI, F_KPHHEI, F_KPHHEII, F_KDISSH2I, F_PHOTOGAMMA,
+  F_XH2SHIELD, F_ISRF, F_FSHIELD_CUSTOM,
+  NFIELD
+};
+
+// Everything a kernel needs, passed by value as a __grid_constant__ parameter.
+// Mirrors the argument list of solve_rate_cool_g (solve_rate_cool_g.F:6-50).
+struct GrParams {
+  // geometry
+  int in, jn, kn, is, js, ks, ie, je, ke;
+  long long nactive;
+  // flags
+  int icool, ispecies, imetal, imcool, idust, idustall, idustfield, idustrec, igammah, iexpand;
+  int ih2co, ipiht, ih2optical, iciecool, ithreebody, icmbTfloor, iClHeat, clnew;
+  int iH2shield, iradshield, iradtrans, iradcoupled, iradstep, irt_honly;
+  int iVheat, iMheat, iisrffield, iH2shieldcustom, itmax, exititmax;
+  int nratec, ndratec;
+  // scalars
+  double dx, dt, aye, temstart, temend, utem, uxyz, uaye, urho, utim;
+  double gamma, fh, dtoh, z_solar, fgr, dtemstart, dtemend, clEleFra;
+  double k24, k25, k26, k27, k28, k29, k30, k31;
+  double compa, gammaha, isrf, gamma_isrfa, comp_xraya, comp_temp, piHI, piHeI, piHeII;
+  double avgsighi, avgsighei, avgsigheii;
+  // derived once per call on the host (solve_rate_cool_g.F:331-343, cool1d_multi_g.F:179-198)
+  double dom, dom_inv, tbase1, xbase1, dbase1, coolunit, uvel, chunit, dx_cgs, c_ljeans;
+  double zr, comp1, comp2, logtem0, logtem9, dlogtem, d_logtem0, d_logtem9, d_dlogtem;
+  double a3, a3inv;                  // comoving <-> proper factors (aye^3, aye^-3)
+  // Rahmati+13 cell-invariant factors: 6.73e-3*(sig/2.49e-18)^(-2/3) and (k/tbase1/1e-12)^(2/3)
+  double ssh_sig_hi, ssh_sig_hei, ssh_k24, ssh_k26;
+  // tables
+  const double *chem;      // [nratec][NCHEM]
+  const double *cool;      // [nratec][NCOOL]
+  const double *h2dust;    // [ndratec][nratec]
+  const double *k13a;      // raw k13, k22 columns for the H-equilibrium limiter (:606-630)
+  const double *k22a;
+  GrCloudyDev pri, met;
+  // fields (device pointers; NULL when the physics that reads them is off)
+  double *f[NFIELD];
+  double *out;             // calculate_* output
+  // diagnostics: [0]=sum subcycles [1]=max subcycles [2]=#hit itmax [3]=#NaN
+  unsigned long long *diag;
+  // dynamic work queue for the lane-refill solver
+  unsigned long long *work_counter;
+};
+
+#endif

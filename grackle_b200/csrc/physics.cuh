@@ -1,0 +1,255 @@
+// grackle-b200: per-cell physics as sm_100a device code.  One thread owns one cell and
+// keeps its whole state in registers; there are no row temporaries and no masks.
+//
+// Every function names the reference routine whose result it must reproduce.
+// Floating-point operation ORDER is kept where it feeds parity-critical outputs; the
+// structure (per-cell, packed table rows, hoisted cell-invariant factors) is ours.
+#ifndef GRB200_PHYSICS_CUH
+#define GRB200_PHYSICS_CUH
+
+#include "gr_device.h"
+
+namespace grb {
+
+// FLOAT_8 constants of the Fortran side (phys_const.def, grackle_fortran_types.def)
+#define GRB_KBOLTZ 1.3806504e-16
+#define GRB_MASS_H 1.67262171e-24
+#define GRB_SIGMA_SB 5.670373e-5
+#define GRB_TINY 1.0e-20
+#define GRB_TINY8 1.0e-40
+#define GRB_HUGE8 1.0e40
+#define GRB_MU_METAL 16.0
+
+__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
+__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+__device__ __forceinline__ long long imin(long long a, long long b) { return a < b ? a : b; }
+__device__ __forceinline__ long long imax(long long a, long long b) { return a > b ? a : b; }
+__device__ __forceinline__ double ld(const double *p) { return __ldg(p); }
+__device__ __forceinline__ double sq(double x) { return x * x; }
+__device__ __forceinline__ double pow4(double x) { const double x2 = x * x; return x2 * x2; }
+
+// 1-based clamped index on a uniform axis (interpolators_g.F:28-29 and friends)
+__device__ __forceinline__ long long axis_index(double x, const double *par, double dpar, long long n)
+{
+  return imin(n - 1, imax(1, (long long)((x - ld(par)) / dpar) + 1));
+}
+
+// linear interpolation along the last (fastest) axis starting at flat 1-based index `at`
+__device__ __forceinline__ double lerp_last(const double *data, long long at, double x,
+                                            double x0, double x1)
+{
+  const double v0 = ld(data + at - 1), v1 = ld(data + at);
+  const double slope = (v1 - v0) / (x1 - x0);
+  return (x - x0) * slope + v0;
+}
+
+// ---- interpolate_1D_g / 2D / 3D / 3Dz / 2Df3D (interpolators_g.F:4-338) ----------
+__device__ inline double interp1(const GrCloudyDev &c, const double *data, double in1)
+{
+  const long long i1 = axis_index(in1, c.par[0], c.dpar[0], c.dim[0]);
+  return lerp_last(data, i1, in1, ld(c.par[0] + i1 - 1), ld(c.par[0] + i1));
+}
+
+__device__ inline double interp2(const GrCloudyDev &c, const double *data, double in1, double in2)
+{
+  const long long i1 = axis_index(in1, c.par[0], c.dpar[0], c.dim[0]);
+  const long long i2 = axis_index(in2, c.par[1], c.dpar[1], c.dim[1]);
+  const double x0 = ld(c.par[1] + i2 - 1), x1 = ld(c.par[1] + i2);
+  double v[2];
+#pragma unroll
+  for (int q = 1; q <= 2; q++)
+    v[q - 1] = lerp_last(data, (q + i1 - 2) * c.dim[1] + i2, in2, x0, x1);
+  const double slope = (v[1] - v[0]) / (ld(c.par[0] + i1) - ld(c.par[0] + i1 - 1));
+  return (in1 - ld(c.par[0] + i1 - 1)) * slope + v[0];
+}
+
+__device__ inline double interp3(const GrCloudyDev &c, const double *data, double in1, double in2,
+                                 double in3)
+{
+  const long long i1 = axis_index(in1, c.par[0], c.dpar[0], c.dim[0]);
+  const long long i2 = axis_index(in2, c.par[1], c.dpar[1], c.dim[1]);
+  const long long i3 = axis_index(in3, c.par[2], c.dpar[2], c.dim[2]);
+  const double x0 = ld(c.par[2] + i3 - 1), x1 = ld(c.par[2] + i3);
+  const double y0 = ld(c.par[1] + i2 - 1), y1 = ld(c.par[1] + i2);
+  double v2[2];
+#pragma unroll
+  for (int q = 1; q <= 2; q++) {
+    double v3[2];
+#pragma unroll
+    for (int w = 1; w <= 2; w++)
+      v3[w - 1] = lerp_last(data, ((q + i1 - 2) * c.dim[1] + (w + i2 - 2)) * c.dim[2] + i3, in3, x0, x1);
+    const double slope = (v3[1] - v3[0]) / (y1 - y0);
+    v2[q - 1] = (in2 - y0) * slope + v3[0];
+  }
+  const double slope = (v2[1] - v2[0]) / (ld(c.par[0] + i1) - ld(c.par[0] + i1 - 1));
+  return (in1 - ld(c.par[0] + i1 - 1)) * slope + v2[0];
+}
+
+// rank-3 (n_H, z, T) grid: linear in log(1+z) with the host-located z index
+__device__ inline double interp3z(const GrCloudyDev &c, const double *data, double in1, double zr,
+                                  double in3)
+{
+  const long long i1 = axis_index(in1, c.par[0], c.dpar[0], c.dim[0]);
+  const long long i3 = axis_index(in3, c.par[2], c.dpar[2], c.dim[2]);
+  const long long i2 = c.zindex;
+  const double x0 = ld(c.par[2] + i3 - 1), x1 = ld(c.par[2] + i3);
+  const double p0 = ld(c.par[0] + i1 - 1), p1 = ld(c.par[0] + i1);
+  if (c.end_int) {                       // interpolate_2Df3D_g
+    double v[2];
+#pragma unroll
+    for (int q = 1; q <= 2; q++)
+      v[q - 1] = lerp_last(data, ((q + i1 - 2) * c.dim[1] + (i2 - 1)) * c.dim[2] + i3, in3, x0, x1);
+    const double slope = (v[1] - v[0]) / (p1 - p0);
+    return (in1 - p0) * slope + v[0];
+  }
+  const double z0 = ld(c.par[1] + i2 - 1), z1 = ld(c.par[1] + i2);
+  const double zden = log((1 + z1) / (1 + z0));
+  const double znum = log((1 + zr) / (1 + z0));
+  double v2[2];
+#pragma unroll
+  for (int q = 1; q <= 2; q++) {
+    double v3[2];
+#pragma unroll
+    for (int w = 1; w <= 2; w++)
+      v3[w - 1] = lerp_last(data, ((q + i1 - 2) * c.dim[1] + (w + i2 - 2)) * c.dim[2] + i3, in3, x0, x1);
+    const double slope = (v3[1] - v3[0]) / zden;
+    v2[q - 1] = znum * slope + v3[0];
+  }
+  const double slope = (v2[1] - v2[0]) / (p1 - p0);
+  return (in1 - p0) * slope + v2[0];
+}
+
+// rank dispatch for new-style tables (cool1d_cloudy_g.F:157-236)
+__device__ inline double cloudy_lookup(const GrCloudyDev &c, const double *data, double log_n_h,
+                                       double zr, double log10T)
+{
+  if (c.rank == 1) return interp1(c, data, log10T);
+  if (c.rank == 2) return interp2(c, data, log_n_h, log10T);
+  return interp3z(c, data, log_n_h, zr, log10T);
+}
+
+// ---- cool1d_cloudy_g (cool1d_cloudy_g.F:4-261): returns the edot increment -------
+__device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, double rhoH,
+                                     double metallicity, double logtem, int icmbTfloor, int iZscale)
+{
+  const double inv_log10 = 1.0 / log(10.0);
+  const double log10_tCMB = log10(P.comp2);
+  const double log10tem = logtem * inv_log10;
+  const double log_n_h = log10(rhoH * P.dom);
+  double edot_met = -pow(10.0, cloudy_lookup(c, c.cooling, log_n_h, P.zr, log10tem));
+  if (icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
+    edot_met = edot_met + pow(10.0, cloudy_lookup(c, c.cooling, log_n_h, P.zr, log10_tCMB));
+  if (c.get_heat == 1)
+    edot_met = edot_met + pow(10.0, cloudy_lookup(c, c.heating, log_n_h, P.zr, log10tem));
+  if (iZscale == 1) edot_met = edot_met * metallicity;
+  return edot_met * rhoH * rhoH;
+}
+
+// ---- old-style tables, rank <= 3 (cool1d_cloudy_old_tables_g.F; rank 4/5 need the
+// electron-fraction axis and are rejected on the host) ----------------------------
+__device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c, double d,
+                                         double rhoH, double metallicity, double logtem)
+{
+  const double inv_log10 = 1.0 / log(10.0);
+  const double log10_tCMB = log10(P.comp2);      // see oracle note on the unassigned upstream local
+  const double log10tem = logtem * inv_log10;
+  double log_n_h = 0.0, log_Z = 0.0;
+  if (c.rank > 1) log_n_h = log10(rhoH * P.dom);
+  if (c.rank > 2) log_Z = log10(metallicity);
+  auto look = [&](const double *data, double lt) {
+    if (c.rank == 1) return interp1(c, data, lt);
+    if (c.rank == 2) return interp2(c, data, log_n_h, lt);
+    return interp3(c, data, log_n_h, log_Z, lt);
+  };
+  double edot_met = -pow(10.0, look(c.cooling, log10tem));
+  if (P.icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
+    edot_met = edot_met + pow(10.0, look(c.cooling, log10_tCMB));
+  if (P.iClHeat == 1) edot_met = edot_met + pow(10.0, look(c.heating, log10tem));
+  return edot_met * rhoH * d;
+}
+
+// ---- calc_temp1d_cloudy_g (calc_temp1d_cloudy_g.F:150-242): T and mu for pc=0 -----
+__device__ inline void temperature_table(const GrParams &P, double d, double e, double metal,
+                                         double rhoH, double &tgas, double &mmw)
+{
+  const GrCloudyDev &c = P.pri;
+  const double inv_log10 = 1.0 / log(10.0);
+  const double log_n_h = log10(rhoH * P.dom);
+  double munew = 1.0, muold = 1.0;
+  for (int ti = 1; ti <= 20; ti++) {
+    muold = munew;
+    tgas = dmax((P.gamma - 1.0) * e * munew * P.utem, P.temstart);
+    const double log10tem = log(tgas) * inv_log10;
+    munew = cloudy_lookup(c, c.mmw, log_n_h, P.zr, log10tem);
+    munew = 0.5 * (munew + muold);
+    tgas = tgas * munew / muold;
+    if (fabs((munew / muold) - 1.0) <= 1.e-2) {
+      muold = munew;
+      if (P.imetal == 1) {
+        munew = d / ((d - metal) / munew + metal / GRB_MU_METAL);
+        tgas = tgas * munew / muold;
+      }
+      break;
+    }
+  }
+  mmw = munew;
+}
+
+// ---- calc_tdust_1d_g + calc_kappa_gr_g + calc_gr_balance_g (calc_tdust_1d_g.F) ----
+__device__ __forceinline__ double kappa_gr(double td)
+{
+  if (td < 200.0) return 4.0e-4 * (td * td);
+  if (td < 1.5e3) return 16.0;
+  const double x3 = ((td / 1.5e3) * (td / 1.5e3)) * (td / 1.5e3);
+  const double x6 = x3 * x3;
+  return dmax(GRB_TINY, 16.0 * (1.0 / (x6 * x6)));
+}
+__device__ __forceinline__ double gr_balance(double td, double tgas, double kgr, double trad4,
+                                             double gasgr, double gamma_isrf, double nh)
+{
+  return gamma_isrf + (4.0 * GRB_SIGMA_SB) * kgr * (trad4 - pow4(td)) + (gasgr * nh * (tgas - td));
+}
+
+__device__ inline double dust_temperature(double tgas, double nh, double gasgr, double gamma_isrfa,
+                                          double isrf, double trad_in)
+{
+  const double t_subl = 1.5e3, radf = 4.0 * GRB_SIGMA_SB, kgr1 = 4.0e-4;
+  const double trad = dmax(1.0, trad_in);
+  const double trad4 = pow4(trad);
+  const double gamma_isrf = isrf * gamma_isrfa;
+  bool newton = true, bisect = true;
+  double td = 0.0, pert = 1.e-3;
+  if (trad >= tgas) {
+    td = trad; newton = false; bisect = false;
+  } else if (tgas > t_subl) {
+    newton = false;
+  } else {
+    td = dmax(trad, pow(gamma_isrf / radf / kgr1, 0.17));
+  }
+  for (int it = 1; it <= 50 && newton; it++) {
+    const double tdp = dmax(1.e-3, ((1.0 + pert) * td));
+    const double sol = gr_balance(td, tgas, kappa_gr(td), trad4, gasgr, gamma_isrf, nh);
+    const double solp = gr_balance(tdp, tgas, kappa_gr(tdp), trad4, gasgr, gamma_isrf, nh);
+    const double slope = (solp - sol) / (pert * td);
+    const double told = td;
+    td = td - (sol / slope);
+    pert = dmax(dmin(pert, (0.5 * fabs(td - told) / td)), 1.e-10);
+    if (td < trad) newton = false;                       // give up, bisection takes over
+    else if (fabs(sol / solp) < 1.e-5) { newton = false; bisect = false; }
+  }
+  if (bisect) {
+    td = trad;
+    double hi = tgas;
+    for (int it = 1; it <= 30; it++) {
+      double mid = 0.5 * (td + hi);
+      if (it == 1) mid = dmin(mid, t_subl);
+      const double sol = gr_balance(mid, tgas, kappa_gr(mid), trad4, gasgr, gamma_isrf, nh);
+      if (sol > 0.0) td = mid; else hi = mid;
+      if ((fabs(hi - td) / td) <= 1.e-3) break;
+    }
+  }
+  return td;
+}
+
+}  // namespace grb
+#endif

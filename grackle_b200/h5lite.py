@@ -220,3 +220,127 @@ def read_file(path):
     r = _Reader(buf)
     root_ohdr = struct.unpack_from("<Q", buf, 56 + 8)[0]
     return r.read_object(r.base + root_ohdr, "/")
+
+
+# --------------------------------------------------------------------------
+# writer (same dialect; used for the synthetic HM2012-schema table and for
+# re-packing fixtures)
+# --------------------------------------------------------------------------
+class Dataset:
+    def __init__(self, data, attrs=None):
+        self.data = data          # numpy array (float64 / int64) or str
+        self.attrs = attrs or {}
+
+
+class Group(dict):
+    """dict name -> Group | Dataset, plus .attrs"""
+    def __init__(self, *a, attrs=None, **k):
+        super().__init__(*a, **k)
+        self.attrs = attrs or {}
+
+
+def _pad8(b):
+    return b + b"\0" * ((-len(b)) % 8)
+
+
+def _dtype_msg(value):
+    if isinstance(value, (str, bytes)):
+        return struct.pack("<BBBBI", 0x13, 0, 0, 0, len(value) + 1)
+    if np.asarray(value).dtype.kind in "iu":     # 64-bit signed big-endian
+        return struct.pack("<BBBBIHH", 0x10, 0x09, 0, 0, 8, 0, 64)
+    # IEEE f64 big-endian
+    return struct.pack("<BBBBIHHBBBBI", 0x11, 0x21, 0x3F, 0, 8, 0, 64, 52, 11, 0, 52, 1023)
+
+
+def _space_msg(value):
+    dims = () if isinstance(value, (str, bytes)) else np.asarray(value).shape
+    return struct.pack("<BBB5x", 1, len(dims), 0) + b"".join(struct.pack("<Q", d) for d in dims)
+
+
+def _raw(value):
+    if isinstance(value, str):
+        return value.encode("latin1") + b"\0"
+    if isinstance(value, bytes):
+        return value + b"\0"
+    a = np.asarray(value)
+    return np.ascontiguousarray(a, dtype=">i8" if a.dtype.kind in "iu" else ">f8").tobytes()
+
+
+def _msg(mtype, body):
+    body = _pad8(body)
+    return struct.pack("<HHB3x", mtype, len(body), 0) + body
+
+
+def _attr_msg(name, value):
+    nm = name.encode("latin1") + b"\0"
+    dt, ds = _dtype_msg(value), _space_msg(value)
+    body = (struct.pack("<BBHHH", 1, 0, len(nm), len(dt), len(ds)) + _pad8(nm) + _pad8(dt) +
+            _pad8(ds) + _raw(value))
+    return _msg(0x0C, body)
+
+
+class _Writer:
+    LEAF_K = 64     # up to 128 links per group in a single symbol-table node
+    INT_K = 16
+
+    def __init__(self):
+        self.buf = bytearray(b"\0" * 96)
+
+    def alloc(self, data):
+        off = len(self.buf)
+        self.buf += _pad8(bytes(data))
+        return off
+
+    def header(self, msgs):
+        body = b"".join(msgs)
+        return self.alloc(struct.pack("<BBHII4x", 1, 0, len(msgs), 1, len(body)) + body)
+
+    def write_dataset(self, ds):
+        raw = _raw(ds.data)
+        addr = self.alloc(raw)
+        msgs = [_msg(0x01, _space_msg(ds.data)), _msg(0x03, _dtype_msg(ds.data)),
+                _msg(0x08, struct.pack("<BBQQ", 3, 1, addr, len(raw)))]
+        msgs += [_attr_msg(k, v) for k, v in ds.attrs.items()]
+        return self.header(msgs)
+
+    def write_group(self, grp):
+        """returns (object header address, btree address, heap address)"""
+        names = sorted(grp.keys())
+        assert len(names) <= 2 * self.LEAF_K, "too many entries for one symbol-table node"
+        child = {}
+        for n in names:
+            node = grp[n]
+            child[n] = self.write_dataset(node) if isinstance(node, Dataset) else self.write_group(node)[0]
+        heap_data = bytearray(b"\0" * 8)         # offset 0 = empty string
+        name_off = {}
+        for n in names:
+            name_off[n] = len(heap_data)
+            heap_data += _pad8(n.encode("latin1") + b"\0")
+        data_addr = self.alloc(heap_data)
+        heap_addr = self.alloc(b"HEAP" + struct.pack("<B3xQQQ", 0, len(heap_data), UNDEF, data_addr))
+        snod = bytearray(b"SNOD" + struct.pack("<BBH", 1, 0, len(names)))
+        for n in names:
+            snod += struct.pack("<QQII16x", name_off[n], child[n], 0, 0)
+        snod += b"\0" * (8 + 2 * self.LEAF_K * 40 - len(snod))
+        snod_addr = self.alloc(snod)
+        tree = bytearray(b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, UNDEF, UNDEF))
+        tree += struct.pack("<QQQ", 0, snod_addr, name_off[names[-1]] if names else 0)
+        tree += b"\0" * (24 + (2 * self.INT_K + 1) * 8 + 2 * self.INT_K * 8 - len(tree))
+        tree_addr = self.alloc(tree)
+        msgs = [_msg(0x11, struct.pack("<QQ", tree_addr, heap_addr))]
+        msgs += [_attr_msg(k, v) for k, v in getattr(grp, "attrs", {}).items()]
+        return self.header(msgs), tree_addr, heap_addr
+
+
+def write_file(path, root):
+    """root: Group.  Writes a superblock-v0 HDF5 file."""
+    w = _Writer()
+    ohdr, tree_addr, heap_addr = w.write_group(root)
+    sb = b"\x89HDF\r\n\x1a\n" + struct.pack("<BBBBBBBBHHI", 0, 0, 0, 0, 0, 8, 8, 0,
+                                              w.LEAF_K, w.INT_K, 0)
+    sb += struct.pack("<QQQQ", 0, UNDEF, len(w.buf), UNDEF)
+    sb += struct.pack("<QQII", 0, ohdr, 1, 0) + struct.pack("<QQ", tree_addr, heap_addr)
+    assert len(sb) == 96
+    w.buf[:96] = sb
+    with open(path, "wb") as f:
+        f.write(bytes(w.buf))
