@@ -73,6 +73,7 @@ struct GrParams {
   int iH2shield, iradshield, iradtrans, iradcoupled, iradstep, irt_honly;
   int iVheat, iMheat, iisrffield, iH2shieldcustom, itmax, exititmax;
   int nratec, ndratec;
+  int scale_div;           // 1: comoving->proper by division (cool_multi_time_g), 0: by multiplication
   // scalars
   double dx, dt, aye, temstart, temend, utem, uxyz, uaye, urho, utim;
   double gamma, fh, dtoh, z_solar, fgr, dtemstart, dtemend, clEleFra;

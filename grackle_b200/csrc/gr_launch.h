@@ -1,0 +1,16 @@
+// grackle-b200: launch entry points of kernels.cu, called from api.cu
+#ifndef GRB200_LAUNCH_H
+#define GRB200_LAUNCH_H
+#include <cuda_runtime.h>
+#include "gr_device.h"
+
+#define GRB_SOLVE_THREADS 128
+
+void grb_launch_thermo(const GrParams &P, int mode, cudaStream_t st);     // 0 p, 1 T, 2 gamma
+void grb_launch_fill(const GrParams &P, double value, cudaStream_t st);
+void grb_launch_temperature_table(const GrParams &P, cudaStream_t st);
+void grb_launch_cooling_time(const GrParams &P, cudaStream_t st);
+void grb_launch_dust_temperature(const GrParams &P, cudaStream_t st);
+void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st);
+int grb_solve_max_blocks_per_sm(int pc);
+#endif

@@ -1,0 +1,488 @@
+// grackle-b200: the sm_100a kernels.  One thread per active cell, whole cell state in
+// registers, SoA fields read/written exactly once per call, comoving<->proper scaling
+// and species floors/renormalisation fused into the same pass.
+//
+//   k_pressure / k_temperature / k_gamma   calculate_{pressure,temperature,gamma}.c   HBM-bound
+//   k_temperature_table                    calc_temp_cloudy_g.F (pc = 0)              HBM + L2 gathers
+//   k_cooling_time                         cool_multi_time_g.F                        HBM + FP64
+//   k_dust_temperature                     calc_tdust_3d_g.F                          FP64 (Newton)
+//   k_solve                                solve_rate_cool_g.F (whole file)           FP64 pipe
+//
+// No tensor cores: there is no dense contraction anywhere on this path (north_star).
+#include <cuda_runtime.h>
+
+#include "network.cuh"
+#include "gr_launch.h"
+
+namespace grb {
+
+// active-cell id -> flat field index (i fastest), plus (i,j,k) when needed
+__device__ __forceinline__ size_t cell_index(const GrParams &P, long long t, int &i, int &j, int &k)
+{
+  const int ni = P.ie - P.is + 1, nj = P.je - P.js + 1;
+  i = (int)(t % ni) + P.is;
+  const long long r = t / ni;
+  j = (int)(r % nj) + P.js;
+  k = (int)(r / nj) + P.ks;
+  return (size_t)i + (size_t)P.in * ((size_t)j + (size_t)P.jn * (size_t)k);
+}
+
+// Load one cell, converting comoving -> proper in registers (scale_fields_g) and applying
+// the species floors (ceiling_species_g) when `floors` is set (solve only).
+template <int PC>
+__device__ __forceinline__ void load_cell(const GrParams &P, size_t x, Cell &c, bool floors)
+{
+  const double s = (P.iexpand == 1) ? P.a3inv : 1.0;
+  const bool sc = (P.iexpand == 1);
+  // solve multiplies by aye**(-3) (solve_rate_cool_g.F:353); cooling time divides by aye**3
+  // (cool_multi_time_g.F:163): keep each spelling so roundings match
+#define LDF(id) (sc ? (P.scale_div ? P.f[id][x] / P.a3 : P.f[id][x] * s) : P.f[id][x])
+  c.d = LDF(F_D);
+  c.e = P.f[F_E][x];
+  c.metal = (P.imetal == 1) ? LDF(F_METAL) : 0.0;
+  c.dust = (P.idustfield == 1) ? LDF(F_DUST) : 0.0;
+  if (PC > 0) {
+    c.de = LDF(F_DE); c.HI = LDF(F_HI); c.HII = LDF(F_HII);
+    c.HeI = LDF(F_HEI); c.HeII = LDF(F_HEII); c.HeIII = LDF(F_HEIII);
+  } else {
+    c.de = c.HI = c.HII = c.HeI = c.HeII = c.HeIII = 0.0;
+  }
+  if (PC > 1) { c.HM = LDF(F_HM); c.H2I = LDF(F_H2I); c.H2II = LDF(F_H2II); }
+  else { c.HM = c.H2I = c.H2II = 0.0; }
+  if (PC > 2) { c.DI = LDF(F_DI); c.DII = LDF(F_DII); c.HDI = LDF(F_HDI); }
+  else { c.DI = c.DII = c.HDI = 0.0; }
+#undef LDF
+  if (floors) {
+    if (PC > 0) {
+      c.de = dmax(c.de, GRB_TINY); c.HI = dmax(c.HI, GRB_TINY); c.HII = dmax(c.HII, GRB_TINY);
+      c.HeI = dmax(c.HeI, GRB_TINY); c.HeII = dmax(c.HeII, GRB_TINY);
+      c.HeIII = dmax(c.HeIII, 1e-5 * GRB_TINY);
+    }
+    if (PC > 1) { c.HM = dmax(c.HM, GRB_TINY); c.H2I = dmax(c.H2I, GRB_TINY); c.H2II = dmax(c.H2II, GRB_TINY); }
+    if (PC > 2) { c.DI = dmax(c.DI, GRB_TINY); c.DII = dmax(c.DII, GRB_TINY); c.HDI = dmax(c.HDI, GRB_TINY); }
+    if (P.imetal == 1) c.metal = dmax(c.metal, GRB_TINY);
+  }
+  c.vheat = (P.iVheat == 1) ? P.f[F_VHEAT][x] : 0.0;
+  c.mheat = (P.iMheat == 1) ? P.f[F_MHEAT][x] : 0.0;
+  c.isrf = (P.iisrffield > 0) ? P.f[F_ISRF][x] : 0.0;
+  if (P.iradtrans == 1) {
+    c.kphHI = P.f[F_KPHHI][x]; c.kphHeI = P.f[F_KPHHEI][x]; c.kphHeII = P.f[F_KPHHEII][x];
+    c.photogamma = P.f[F_PHOTOGAMMA][x];
+    c.kdissH2I = (PC > 1) ? P.f[F_KDISSH2I][x] : 0.0;
+  } else {
+    c.kphHI = c.kphHeI = c.kphHeII = c.photogamma = c.kdissH2I = 0.0;
+  }
+  c.xH2shield = (PC > 1 && P.iH2shield == 2) ? P.f[F_XH2SHIELD][x] : 0.0;
+  c.fshield = (PC > 1 && P.iH2shieldcustom > 0) ? P.f[F_FSHIELD_CUSTOM][x] : 1.0;
+}
+
+// ------------------------------------------------------------------------------
+// calculate_pressure / temperature / gamma  (pc > 0; proper or comoving alike: these
+// routines never rescale, calculate_pressure.c:31-128, calculate_temperature.c:64-148,
+// calculate_gamma.c:37-124).  MODE 0 = pressure, 1 = temperature, 2 = gamma.
+// ------------------------------------------------------------------------------
+template <int PC, int MODE>
+__global__ void __launch_bounds__(256) k_thermo(const __grid_constant__ GrParams P)
+{
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= P.nactive) return;
+  int i, j, k;
+  const size_t x = cell_index(P, t, i, j, k);
+  const double tiny_number = 1.e-20;
+  const double d = P.f[F_D][x], e = P.f[F_E][x];
+  double p = ((P.gamma - 1.0) * d * e);
+  if (p < tiny_number) p = tiny_number;
+
+  double HI = 0, HII = 0, HeI = 0, HeII = 0, HeIII = 0, de = 0, HM = 0, H2I = 0, H2II = 0;
+  if (PC > 0 && (MODE > 0 || PC > 1)) {
+    HI = P.f[F_HI][x]; HII = P.f[F_HII][x]; HeI = P.f[F_HEI][x]; HeII = P.f[F_HEII][x];
+    HeIII = P.f[F_HEIII][x]; de = P.f[F_DE][x];
+  }
+  if (PC > 1) { HM = P.f[F_HM][x]; H2I = P.f[F_H2I][x]; H2II = P.f[F_H2II][x]; }
+
+  if (PC > 1) {   // H2 vibrational correction of the pressure
+    const double GammaInverse = 1.0 / (P.gamma - 1.0);
+    double number_density = 0.25 * (HeI + HeII + HeIII) + HI + HII + HM + de;
+    const double nH2 = 0.5 * (H2I + H2II);
+    if (number_density == 0) number_density = tiny_number;
+    const double temp = dmax(P.utem * p / (number_density + nH2), 1);
+    double GammaH2Inverse = 0.5 * 5.0;
+    if (nH2 / number_density > 1e-3) {
+      const double xx = 6100.0 / temp;
+      if (xx < 10.0) {
+        const double ex = exp(xx);
+        GammaH2Inverse = 0.5 * (5 + 2.0 * xx * xx * ex / ((ex - 1.0) * (ex - 1.0)));
+      }
+    }
+    const double Gamma1 = 1.0 + (nH2 + number_density) / (nH2 * GammaH2Inverse + number_density * GammaInverse);
+    p *= (Gamma1 - 1.0) / (P.gamma - 1.0);
+  }
+  if (MODE == 0) { P.out[x] = p; return; }
+
+  // temperature (quirk Q1: the upstream density floor is the constant 1.-20 = -19, i.e. inert)
+  double number_density = 0.25 * (HeI + HeII + HeIII) + HI + HII + de;
+  if (PC > 1) number_density += HM + 0.5 * (H2I + H2II);
+  if (P.imetal == 1) number_density += P.f[F_METAL][x] * (1.0 / GRB_MU_METAL);
+  double T = p * (P.utem / dmax(number_density, 1. - 20));
+  T = dmax(T, 1.0);
+  if (MODE == 1) { P.out[x] = T; return; }
+
+  // gamma (only reached for PC > 1; PC <= 1 is a host-side fill)
+  const double GammaInverse = 1 / (P.gamma - 1.0);
+  number_density = 0.25 * (HeI + HeII + HeIII) + HI + HII + HM + de;
+  const double nH2 = 0.5 * (H2I + H2II);
+  double GammaH2Inverse = 0.5 * 5.0;
+  if (nH2 / number_density > 1e-3) {
+    const double xx = 6100.0 / T;
+    if (xx < 10.0) {
+      const double ex = exp(xx);
+      GammaH2Inverse = 0.5 * (5 + 2.0 * xx * xx * ex / ((ex - 1.0) * (ex - 1.0)));
+    }
+  }
+  P.out[x] = 1.0 + (nH2 + number_density) / (nH2 * GammaH2Inverse + number_density * GammaInverse);
+}
+
+// constant fill of the active region (calculate_gamma for pc <= 1)
+__global__ void __launch_bounds__(256) k_fill(const __grid_constant__ GrParams P, double value)
+{
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= P.nactive) return;
+  int i, j, k;
+  P.out[cell_index(P, t, i, j, k)] = value;
+}
+
+// calc_temp_cloudy_g.F:141-171 (pc = 0).  NB rhoH = fh*d here, without the metal
+// subtraction cool1d_multi_g applies.
+__global__ void __launch_bounds__(256) k_temperature_table(const __grid_constant__ GrParams P)
+{
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= P.nactive) return;
+  int i, j, k;
+  const size_t x = cell_index(P, t, i, j, k);
+  const double s = (P.iexpand == 1) ? P.a3inv : 1.0;
+  const double d = (P.iexpand == 1) ? P.f[F_D][x] * s : P.f[F_D][x];
+  const double metal = (P.imetal == 1) ? ((P.iexpand == 1) ? P.f[F_METAL][x] * s : P.f[F_METAL][x]) : 0.0;
+  double tgas, mmw;
+  temperature_table(P, d, P.f[F_E][x], metal, P.fh * d, tgas, mmw);
+  P.out[x] = tgas;
+}
+
+// cool_multi_time_g.F: one cool_rate evaluation, t_cool = max(p/(gamma-1), tiny)/edot
+template <int PC>
+__global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ GrParams P)
+{
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= P.nactive) return;
+  int i, j, k;
+  const size_t x = cell_index(P, t, i, j, k);
+  Cell c;
+  load_cell<PC>(P, x, c, false);
+  Thermo th;
+  double tgasold = 0.0;
+  cool_rate<PC>(P, c, true, tgasold, th);
+  const double energy = dmax(th.p2d / (P.gamma - 1.0), GRB_TINY);
+  P.out[x] = energy / th.edot;
+}
+
+// calc_tdust_3d_g.F: gas temperature comes in through P.f[F_VHEAT] (scratch slot)
+template <int PC>
+__global__ void __launch_bounds__(128) k_dust_temperature(const __grid_constant__ GrParams P)
+{
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= P.nactive) return;
+  int i, j, k;
+  const size_t x = cell_index(P, t, i, j, k);
+  const double myisrf = (P.iisrffield > 0) ? P.f[F_ISRF][x] : P.isrf;
+  double nh = P.f[F_HI][x] + P.f[F_HII][x];
+  if (PC > 1) nh = nh + P.f[F_H2I][x] + P.f[F_H2II][x];
+  nh = nh * P.urho / GRB_MASS_H;
+  const double tgas = P.f[F_VHEAT][x];
+  double logtem = log(tgas);
+  logtem = dmax(logtem, P.logtem0);
+  logtem = dmin(logtem, P.logtem9);
+  const TIndex ti = t_index(P, logtem);
+  const double *row = P.cool + (size_t)(ti.idx - 1) * NCOOL;
+  double gasgr = lerp_row(row, NCOOL, L_GASGR, ti.tdef);
+  gasgr = gasgr * P.fgr * P.coolunit / GRB_MASS_H;
+  P.out[x] = dust_temperature(tgas, nh, gasgr, P.gamma_isrfa, myisrf, P.comp2);
+}
+
+// ------------------------------------------------------------------------------
+// k_solve: solve_rate_cool_g.F for every active cell.
+//
+// Divergence control ("lane refill"): subcycle counts differ by orders of magnitude
+// between cells, so a static thread<->cell mapping would leave most lanes of a warp idle
+// while the slowest cell finishes (the reference's OpenMP rows have the same problem).
+// Here a lane that finishes its cell immediately takes the next unprocessed cell from a
+// global queue (one warp-aggregated atomicAdd per refill, found with __ballot_sync), so
+// every lane executes useful subcycles until the queue is empty.  Each cell keeps its own
+// iteration counter, hence the iter==1 / iter>50 heuristics of the reference are
+// reproduced exactly and results do not depend on which lane processed a cell.
+// ------------------------------------------------------------------------------
+struct SubState {           // per-cell carry between subcycles
+  double ttot, tgasold, dedot_prev, HIdot_prev;
+  int iter;
+};
+
+// one subcycle of solve_rate_cool_g.F:451-817 for one cell; returns true when the cell
+// has reached dt
+template <int PC>
+__device__ __forceinline__ bool subcycle(const GrParams &P, Cell &c, SubState &s, size_t x,
+                                         int ci, int cj, int ck)
+{
+  const double dt = P.dt;
+  double dtit = GRB_HUGE8;
+  Thermo th;
+  cool_rate<PC>(P, c, s.iter == 1, s.tgasold, th);
+  double edot = th.edot;
+
+  Rates r;
+  if (PC > 0) {
+    Neigh nb;
+    if (PC > 1 && P.iH2shield == 1) {
+      const double sc = (P.iexpand == 1) ? P.a3inv : 1.0;
+      const size_t sj = (size_t)P.in, sk = (size_t)P.in * P.jn;
+      const double *D = P.f[F_D];
+      nb.d[0] = D[x + 1] * sc; nb.d[1] = D[x - 1] * sc; nb.d[2] = D[x + sj] * sc;
+      nb.d[3] = D[x - sj] * sc; nb.d[4] = D[x + sk] * sc; nb.d[5] = D[x - sk] * sc;
+      (void)ci; (void)cj; (void)ck;
+    }
+    lookup_rates<PC>(P, c, th, nb, r);
+    double dedot, HIdot;
+    rate_derivs<PC>(P, c, th, r, dedot, HIdot, edot);
+
+    // solve_rate_cool_g.F:554-646
+    if (fabs(dedot) < GRB_TINY8) dedot = dmin(GRB_TINY, c.de);
+    if (fabs(HIdot) < GRB_TINY8) HIdot = dmin(GRB_TINY, c.HI);
+    if (dmin(fabs(r.k1 * c.de * c.HI), fabs(r.k2 * c.HII * c.de)) / dmax(fabs(dedot), fabs(HIdot)) > 1.0e6) {
+      dedot = GRB_TINY8;
+      HIdot = GRB_TINY8;
+    }
+    if (s.iter > 50) {
+      dedot = dmin(fabs(dedot), fabs(s.dedot_prev));
+      HIdot = dmin(fabs(HIdot), fabs(s.HIdot_prev));
+    }
+    dtit = dmin(dmin(fabs(0.1 * c.de / dedot), fabs(0.1 * c.HI / HIdot)), dmin(dt - s.ttot, 0.5 * dt));
+
+    if (PC > 1 && c.d * P.dom > 1e8 && edot > 0.0) {
+      // keep the 3-body equilibrium H abundance from changing by more than 10 %
+      const double fd = P.fh * c.d;
+      const double k22lo = ld(P.k22a + r.idx - 1), k22hi = ld(P.k22a + r.idx);
+      const double k13lo = ld(P.k13a + r.idx - 1), k13hi = ld(P.k13a + r.idx);
+      const double eqt2 = dmin(log(th.tgas) + 0.1 * P.dlogtem, r.t2);
+      double eqtdef = (eqt2 - r.t1) / (r.t2 - r.t1);
+      const double eqk222 = k22lo + (k22hi - k22lo) * eqtdef;
+      const double eqk132 = k13lo + (k13hi - k13lo) * eqtdef;
+      const double heq2 = (-1.0 / (4.0 * eqk222)) * (eqk132 - sqrt(8.0 * eqk132 * eqk222 * fd + eqk132 * eqk132));
+      const double eqt1 = dmax(log(th.tgas) - 0.1 * P.dlogtem, r.t1);
+      eqtdef = (eqt1 - r.t1) / (r.t2 - r.t1);
+      const double eqk221 = k22lo + (k22hi - k22lo) * eqtdef;
+      const double eqk131 = k13lo + (k13hi - k13lo) * eqtdef;
+      const double heq1 = (-1.0 / (4.0 * eqk221)) * (eqk131 - sqrt(8.0 * eqk131 * eqk221 * fd + eqk131 * eqk131));
+      const double dheq = (fabs(heq2 - heq1) / (exp(eqt2) - exp(eqt1))) * (th.tgas / th.p2d) * edot;
+      const double heq = (-1.0 / (4.0 * r.k22)) * (r.k13 - sqrt(8.0 * r.k13 * r.k22 * fd + r.k13 * r.k13));
+      dtit = dmin(dtit, 0.1 * heq / dheq);
+    }
+    // (the reference's iter>10 rule min(1.5*olddtit, dtit) is inert: olddtit is always huge8)
+  }
+
+  // cooling/heating limit (:698-750)
+  const double energy = dmax(th.p2d / (P.gamma - 1.0), GRB_TINY8);
+  if (th.tgas <= 1.01 * P.temstart && edot < 0.0) edot = GRB_TINY8;
+  if (fabs(edot) < GRB_TINY8) edot = GRB_TINY8;
+  dtit = dmin(dmin(fabs(0.1 * energy / edot), dt - s.ttot), dtit);
+
+  if (P.icool == 1) c.e = c.e + edot / c.d * dtit;
+  if (PC > 0) step_species<PC>(P, c, th, r, dtit, s.HIdot_prev, s.dedot_prev);
+
+  s.ttot = dmin(s.ttot + dtit, dt);
+  return fabs(dt - s.ttot) < 1.0e-10 * dt;
+}
+
+// extras that are only read when their physics is on are re-fetched per subcycle so they
+// do not occupy registers across the loop
+template <int PC>
+__device__ __forceinline__ void load_extras(const GrParams &P, size_t x, Cell &c)
+{
+  c.vheat = (P.iVheat == 1) ? P.f[F_VHEAT][x] : 0.0;
+  c.mheat = (P.iMheat == 1) ? P.f[F_MHEAT][x] : 0.0;
+  c.isrf = (P.iisrffield > 0) ? P.f[F_ISRF][x] : 0.0;
+  if (P.iradtrans == 1) {
+    c.kphHI = P.f[F_KPHHI][x]; c.kphHeI = P.f[F_KPHHEI][x]; c.kphHeII = P.f[F_KPHHEII][x];
+    c.photogamma = P.f[F_PHOTOGAMMA][x];
+    c.kdissH2I = (PC > 1) ? P.f[F_KDISSH2I][x] : 0.0;
+  } else {
+    c.kphHI = c.kphHeI = c.kphHeII = c.photogamma = c.kdissH2I = 0.0;
+  }
+  c.xH2shield = (PC > 1 && P.iH2shield == 2) ? P.f[F_XH2SHIELD][x] : 0.0;
+  c.fshield = (PC > 1 && P.iH2shieldcustom > 0) ? P.f[F_FSHIELD_CUSTOM][x] : 1.0;
+}
+
+// finished cell -> memory: proper -> comoving, make_consistent_g, store species + energy
+template <int PC>
+__device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
+{
+  if (P.iexpand == 1) {
+    const double s = P.a3;
+    c.d *= s; c.metal *= s;
+    if (PC > 0) { c.de *= s; c.HI *= s; c.HII *= s; c.HeI *= s; c.HeII *= s; c.HeIII *= s; }
+    if (PC > 1) { c.HM *= s; c.H2I *= s; c.H2II *= s; }
+    if (PC > 2) { c.DI *= s; c.DII *= s; c.HDI *= s; }
+  }
+  if (PC > 0) make_consistent<PC>(P, c);
+  P.f[F_E][x] = c.e;
+  if (PC > 0) {
+    P.f[F_DE][x] = c.de; P.f[F_HI][x] = c.HI; P.f[F_HII][x] = c.HII;
+    P.f[F_HEI][x] = c.HeI; P.f[F_HEII][x] = c.HeII; P.f[F_HEIII][x] = c.HeIII;
+  }
+  if (PC > 1) { P.f[F_HM][x] = c.HM; P.f[F_H2I][x] = c.H2I; P.f[F_H2II][x] = c.H2II; }
+  if (PC > 2) { P.f[F_DI][x] = c.DI; P.f[F_DII][x] = c.DII; P.f[F_HDI][x] = c.HDI; }
+}
+
+template <int PC>
+__global__ void __launch_bounds__(GRB_SOLVE_THREADS, 1) k_solve(const __grid_constant__ GrParams P)
+{
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  Cell c;
+  SubState s;
+  size_t x = 0;
+  int ci = 0, cj = 0, ck = 0;
+  bool active = false, exhausted = false;
+  unsigned long long my_sub = 0, my_max = 0, my_itmax = 0, my_nan = 0;
+
+  for (;;) {
+    // ---- refill idle lanes from the global queue ----
+    const unsigned need = __ballot_sync(full, !active && !exhausted);
+    if (need) {
+      unsigned long long base = 0;
+      const int leader = __ffs(need) - 1;
+      if (lane == leader) base = atomicAdd(P.work_counter, (unsigned long long)__popc(need));
+      base = __shfl_sync(full, base, leader);
+      if (!active && !exhausted) {
+        const long long t = (long long)(base + __popc(need & ((1u << lane) - 1)));
+        if (t < P.nactive) {
+          x = cell_index(P, t, ci, cj, ck);
+          bool run = true;
+          if (P.iradtrans == 1 && P.iradcoupled == 1) {   // coupled-RT masks (:418-439)
+            const bool lit = P.f[F_KPHHI][x] > 0;
+            run = (P.iradstep == 1) ? lit : !lit;
+          }
+          load_cell<PC>(P, x, c, true);
+          s.ttot = 0.0; s.tgasold = 0.0; s.dedot_prev = 0.0; s.HIdot_prev = 0.0; s.iter = 1;
+          if (run) active = true;
+          else store_cell<PC>(P, x, c);     // masked cell: floors + consistency only
+        } else {
+          exhausted = true;
+        }
+      }
+    }
+    if (__ballot_sync(full, active) == 0) {
+      if (__ballot_sync(full, !exhausted) == 0) break;
+      continue;
+    }
+    // ---- one subcycle on every busy lane ----
+    if (active) {
+      load_extras<PC>(P, x, c);
+      const bool done = subcycle<PC>(P, c, s, x, ci, cj, ck);
+      my_sub++;
+      if (done || s.iter >= P.itmax) {
+        if (!done) my_itmax++;
+        if (s.iter > (int)my_max) my_max = s.iter;
+        if (!(c.e == c.e) || !(c.HI == c.HI)) my_nan++;
+        store_cell<PC>(P, x, c);
+        active = false;
+      } else {
+        s.iter++;
+      }
+    }
+  }
+
+  // ---- diagnostics: warp reduce, one atomic per warp ----
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    my_sub += __shfl_xor_sync(full, my_sub, o);
+    my_itmax += __shfl_xor_sync(full, my_itmax, o);
+    my_nan += __shfl_xor_sync(full, my_nan, o);
+    const unsigned long long m = __shfl_xor_sync(full, my_max, o);
+    my_max = m > my_max ? m : my_max;
+  }
+  if (lane == 0) {
+    atomicAdd(P.diag + 0, my_sub);
+    atomicMax(P.diag + 1, my_max);
+    if (my_itmax) atomicAdd(P.diag + 2, my_itmax);
+    if (my_nan) atomicAdd(P.diag + 3, my_nan);
+  }
+}
+
+// ------------------------------------------------------------------------------
+// host-callable launchers (declared in gr_launch.h)
+// ------------------------------------------------------------------------------
+static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+}  // namespace grb
+
+using namespace grb;
+
+#define DISPATCH_PC(pc, CALL)                 \
+  switch (pc) {                               \
+    case 0: { CALL(0); break; }               \
+    case 1: { CALL(1); break; }               \
+    case 2: { CALL(2); break; }               \
+    default: { CALL(3); break; }              \
+  }
+
+void grb_launch_thermo(const GrParams &P, int mode, cudaStream_t st)
+{
+  const unsigned nb = blocks_for(P.nactive, 256);
+#define CALL(PCV)                                                              \
+  if (mode == 0) k_thermo<PCV, 0><<<nb, 256, 0, st>>>(P);                      \
+  else if (mode == 1) k_thermo<PCV, 1><<<nb, 256, 0, st>>>(P);                 \
+  else k_thermo<PCV, 2><<<nb, 256, 0, st>>>(P);
+  DISPATCH_PC(P.ispecies, CALL)
+#undef CALL
+}
+
+void grb_launch_fill(const GrParams &P, double value, cudaStream_t st)
+{
+  k_fill<<<blocks_for(P.nactive, 256), 256, 0, st>>>(P, value);
+}
+
+void grb_launch_temperature_table(const GrParams &P, cudaStream_t st)
+{
+  k_temperature_table<<<blocks_for(P.nactive, 256), 256, 0, st>>>(P);
+}
+
+void grb_launch_cooling_time(const GrParams &P, cudaStream_t st)
+{
+  const unsigned nb = blocks_for(P.nactive, 128);
+#define CALL(PCV) k_cooling_time<PCV><<<nb, 128, 0, st>>>(P);
+  DISPATCH_PC(P.ispecies, CALL)
+#undef CALL
+}
+
+void grb_launch_dust_temperature(const GrParams &P, cudaStream_t st)
+{
+  const unsigned nb = blocks_for(P.nactive, 128);
+#define CALL(PCV) k_dust_temperature<PCV><<<nb, 128, 0, st>>>(P);
+  DISPATCH_PC(P.ispecies, CALL)
+#undef CALL
+}
+
+// persistent launch: `blocks` CTAs of GRB_SOLVE_THREADS threads (host picks a multiple of
+// the SM count); P.work_counter must be zero
+void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
+{
+#define CALL(PCV) k_solve<PCV><<<blocks, GRB_SOLVE_THREADS, 0, st>>>(P);
+  DISPATCH_PC(P.ispecies, CALL)
+#undef CALL
+}
+
+int grb_solve_max_blocks_per_sm(int pc)
+{
+  int n = 0;
+#define CALL(PCV) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV>, GRB_SOLVE_THREADS, 0);
+  DISPATCH_PC(pc, CALL)
+#undef CALL
+  return n;
+}
