@@ -751,6 +751,36 @@ double grb200_last_kernel_ms(chemistry_data_storage *rates)
 
 long long grb200_kernel_launch_count(void) { return g_launches.load(); }
 
+// measured FP64 (non-tensor) FMA throughput of the current device in TFLOP/s; <0 on error
+double grb200_measure_fp64_tflops(void)
+{
+  if (!device_ok()) return -1.0;
+  cudaDeviceProp prop;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return -1.0;
+  double *sink = nullptr;
+  if (cudaMalloc(&sink, 64) != cudaSuccess) return -1.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int blocks = prop.multiProcessorCount * 8;
+  grb_launch_fp64_peak(sink, blocks, 2000, 0);            // warm-up
+  cudaDeviceSynchronize();
+  double best = -1.0;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(e0, 0);
+    const double flops = grb_launch_fp64_peak(sink, blocks, 20000, 0);
+    cudaEventRecord(e1, 0);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double tf = flops / (ms * 1e-3) / 1e12;
+    if (tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(sink);
+  return best;
+}
+
 int grb200_device_available(void) { return device_ok() ? 1 : 0; }
 
 }  // extern "C"

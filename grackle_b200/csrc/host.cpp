@@ -177,7 +177,7 @@ int gr_update_uvb_rates(const chemistry_data *chem, const chemistry_data_storage
   const double aprod = units->a_value * units->a_units;
   const double tbase1 = units->time_units;
   const double xbase1 = co_len / aprod;
-  const double dbase1 = co_den * std::pow(aprod, 3);
+  const double dbase1 = co_den * std::pow(aprod, 3.0);
   const double mh = 1.67262171e-24, ev2erg = 1.60217653e-12;
   // heating rates are tabulated in eV/s, hence the extra 1/ev2erg
   const double cool_units = (std::pow(units->a_units, 5) * xbase1 * xbase1 * mh * mh) /

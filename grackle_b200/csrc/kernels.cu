@@ -416,6 +416,25 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, 1) k_solve(const __grid_con
 }
 
 // ------------------------------------------------------------------------------
+// FP64 FMA-chain microbenchmark: the measured non-tensor FP64 peak that the solve
+// kernel's roofline fraction is quoted against.
+// 8 independent chains per thread, 2 flop per DFMA.
+// ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fp64_peak(double *sink, int iters, double a, double b)
+{
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+      x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+    }
+  }
+  const double r = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (r == 123.456) sink[0] = r;      // never true; keeps the chains alive
+}
+
+// ------------------------------------------------------------------------------
 // host-callable launchers (declared in gr_launch.h)
 // ------------------------------------------------------------------------------
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
@@ -485,4 +504,11 @@ int grb_solve_max_blocks_per_sm(int pc)
   DISPATCH_PC(pc, CALL)
 #undef CALL
   return n;
+}
+
+// returns flops issued by one launch
+double grb_launch_fp64_peak(double *sink, int blocks, int iters, cudaStream_t st)
+{
+  k_fp64_peak<<<blocks, 256, 0, st>>>(sink, iters, 0.999999, 1e-9);
+  return (double)blocks * 256.0 * (double)iters * 64.0 * 2.0;
 }

@@ -33,7 +33,7 @@ inline double series(double x, const double (&c)[N])
 {
   double s = c[0];
   if (N > 1) s += c[1] * x;
-  for (int n = 2; n < N; ++n) s += c[n] * std::pow(x, n);
+  for (int n = 2; n < N; ++n) s += c[n] * std::pow(x, (double)n);
   return s;
 }
 
@@ -133,7 +133,7 @@ double r_k9(double T, double u, const Ctx &)
 {
   if (T < 30.0) return 2.10e-20 * std::pow(T / 30.0, -0.15) / u;
   const double l = std::log10(std::fmin(T, 3.2e4));
-  return std::pow(10.0, -18.20 - 3.194 * l + 1.786 * std::pow(l, 2) - 0.2072 * std::pow(l, 3)) / u;
+  return std::pow(10.0, -18.20 - 3.194 * l + 1.786 * std::pow(l, 2) - 0.2072 * std::pow(l, 3.0)) / u;
 }
 
 double r_k10(double, double u, const Ctx &) { return 6.0e-10 / u; }
@@ -182,8 +182,8 @@ double r_k13(double T, double u, const Ctx &cx)
     case 3: k = (1.38e-4 / std::pow(T, 1.025)) * std::exp(-5.2e4 / T); break;
     case 4: {
       const double l = std::log10(T);
-      k = std::pow(1e1, (-178.4239 - 68.42243 * l + 43.20243 * std::pow(l, 2) -
-                         4.633167 * std::pow(l, 3) + 69.70086 * std::log10(1.0 + 40870.38 / T) -
+      k = std::pow(1e1, (-178.4239 - 68.42243 * l + 43.20243 * std::pow(l, 2.0) -
+                         4.633167 * std::pow(l, 3.0) + 69.70086 * std::log10(1.0 + 40870.38 / T) -
                          (23705.7 / T)));
       break;
     }
@@ -215,12 +215,12 @@ void r_k13dd(double T, double u, double out[14])
   const double l = std::log10(T);
   for (int s = 0; s < 2; ++s) {
     const double *f = fit[s];
-    const double a = f[0] + f[1] * l + f[2] * std::pow(l, 2) + f[3] * std::pow(l, 3) +
+    const double a = f[0] + f[1] * l + f[2] * std::pow(l, 2) + f[3] * std::pow(l, 3.0) +
                      f[4] * std::log10(1.0 + f[5] / T);
     const double a1 = f[6] / T;
-    const double b = f[7] + f[8] * l + f[9] * std::pow(l, 2) + f[10] * std::log10(1.0 + f[11] / T);
+    const double b = f[7] + f[8] * l + f[9] * std::pow(l, 2.0) + f[10] * std::log10(1.0 + f[11] / T);
     const double b1 = f[12] / T;
-    const double c = f[13] + f[14] * l + f[15] * std::pow(l, 2) + f[16] / T;
+    const double c = f[13] + f[14] * l + f[15] * std::pow(l, 2.0) + f[16] / T;
     const double c1 = f[17] + c;
     const double d = f[18] + f[19] * std::exp(-T / 1850.0) + f[20] * std::exp(-T / 440.0);
     double *o = out + 7 * s;
@@ -313,7 +313,7 @@ double r_k51(double T, double u, const Ctx &)
 double r_k52(double T, double u, const Ctx &)
 {
   if (T <= 1e4)
-    return 1.0e-9 * (0.417 + 0.846 * std::log10(T) - 0.137 * std::pow(std::log10(T), 2)) / u;
+    return 1.0e-9 * (0.417 + 0.846 * std::log10(T) - 0.137 * std::pow(std::log10(T), 2.0)) / u;
   return 1.609e-9 / u;
 }
 
@@ -332,7 +332,7 @@ double r_k54(double T, double, const Ctx &)
 double r_k55(double T, double u, const Ctx &)
 {
   if (T <= 2.0e2) return 1.08e-22 / u;
-  return 5.25e-11 * std::exp(-4.43e3 / T + 1.739e5 / std::pow(T, 2)) / u;
+  return 5.25e-11 * std::exp(-4.43e3 / T + 1.739e5 / std::pow(T, 2.0)) / u;
 }
 
 double r_k57(double T, double u, const Ctx &)
@@ -444,7 +444,7 @@ double c_reHeIII(double T, double u, const Ctx &cx)
 double c_brem(double T, double u, const Ctx &cx)
 {
   if (cx.p->bremsstrahlung_cooling_rates != 1) return kTiny;
-  return 1.43e-27 * std::sqrt(T) * (1.1 + 0.34 * std::exp(-std::pow(5.5 - std::log10(T), 2) / 3.0)) / u;
+  return 1.43e-27 * std::sqrt(T) * (1.1 + 0.34 * std::exp(-std::pow(5.5 - std::log10(T), 2.0) / 3.0)) / u;
 }
 
 // Lepp & Shull (1983) H2 cooling pieces (tabulated for ABI parity; the kernels use
@@ -452,7 +452,7 @@ double c_brem(double T, double u, const Ctx &cx)
 double ls83_par(double T)
 {
   if (T > 1635.0) return 1.0e-12 * std::sqrt(T) * std::exp(-1000.0 / T);
-  return 1.4e-13 * std::exp((T / 125.0) - std::pow(T / 577.0, 2));
+  return 1.4e-13 * std::exp((T / 125.0) - std::pow(T / 577.0, 2.0));
 }
 double c_vibh(double T, double u, const Ctx &) { return 1.1e-18 * expcap(6744.0 / T) / u; }
 double c_hyd01k(double T, double u, const Ctx &)
@@ -468,27 +468,27 @@ double c_rotl(double T, double u, const Ctx &)
 {
   const double x = std::log10(T / 1.0e4);
   if (T > 4031.0) return 1.38e-22 * std::exp(-9243.0 / T) / u;
-  return std::pow(10.0, -22.9 - 0.553 * x - 1.148 * std::pow(x, 2)) / u;
+  return std::pow(10.0, -22.9 - 0.553 * x - 1.148 * std::pow(x, 2.0)) / u;
 }
 double c_roth(double T, double u, const Ctx &)
 {
   const double x = std::log10(T / 1.0e4);
   if (T > 1087.0) return 3.9e-19 * std::exp(-6118.0 / T) / u;
-  return std::pow(10.0, -19.24 + 0.474 * x - 1.247 * std::pow(x, 2)) / u;
+  return std::pow(10.0, -19.24 + 0.474 * x - 1.247 * std::pow(x, 2.0)) / u;
 }
 
 // Galli & Palla (1998)
 double c_gp99low(double T, double u, const Ctx &)
 {
   const double lt = std::log10(std::fmin(std::fmax(T, 13.0), 1.0e5));
-  return std::pow(10.0, -103.0 + 97.59 * lt - 48.05 * std::pow(lt, 2) + 10.8 * std::pow(lt, 3) -
-                            0.9032 * std::pow(lt, 4)) / u;
+  return std::pow(10.0, -103.0 + 97.59 * lt - 48.05 * std::pow(lt, 2) + 10.8 * std::pow(lt, 3.0) -
+                            0.9032 * std::pow(lt, 4.0)) / u;
 }
 double c_gp99high(double T, double u, const Ctx &)
 {
   const double t3 = std::fmin(std::fmax(T, 13.0), 1.0e5) / 1000.0;
   const double lr = (9.5e-22 * std::pow(t3, 3.76)) / (1.0 + 0.12 * std::pow(t3, 2.1)) *
-                        std::exp(-std::pow((0.13 / t3), 3)) + 3.0e-24 * std::exp(-0.51 / t3);
+                        std::exp(-std::pow((0.13 / t3), 3.0)) + 3.0e-24 * std::exp(-0.51 / t3);
   const double lv = 6.7e-19 * std::exp(-5.86 / t3) + 1.6e-18 * std::exp(-11.7 / t3);
   return (lr + lv) / u;
 }
@@ -581,8 +581,8 @@ double c_hdlow(double T, double u, const Ctx &)
 double cie_thin(double T)
 {
   const int last = kCieCount - 1;
-  if (T <= kCieT[0]) return kCieRate[0] * std::pow(T / kCieT[0], 4);
-  if (T >= kCieT[last]) return kCieRate[last] * std::pow(T / kCieT[last], 3);
+  if (T <= kCieT[0]) return kCieRate[0] * std::pow(T / kCieT[0], 4.0);
+  if (T >= kCieT[last]) return kCieRate[last] * std::pow(T / kCieT[last], 3.0);
   int lo = 0, hi = last;
   while (hi - lo > 1) {           // same midpoint bisection as rate_functions.c:1259-1276
     const int mid = (hi + lo) / 2;
@@ -659,11 +659,11 @@ int gr_build_rate_tables(chemistry_data *chem, chemistry_data_storage *rates, co
   const double aprod = units->a_value * units->a_units;
   const double tbase = units->time_units;
   const double xbase = co_length_units / aprod;
-  const double dbase = co_density_units * std::pow(aprod, 3);
-  const double u_k = (std::pow(units->a_units, 3) * kMh) / (dbase * tbase);
-  const double u_k3 = u_k * (std::pow(units->a_units, 3) * kMh) / dbase;
-  const double u_cool = (std::pow(units->a_units, 5) * std::pow(xbase, 2) * std::pow(kMh, 2)) /
-                        (dbase * std::pow(tbase, 3));
+  const double dbase = co_density_units * std::pow(aprod, 3.0);
+  const double u_k = (std::pow(units->a_units, 3.0) * kMh) / (dbase * tbase);
+  const double u_k3 = u_k * (std::pow(units->a_units, 3.0) * kMh) / dbase;
+  const double u_cool = (std::pow(units->a_units, 5) * std::pow(xbase, 2) * std::pow(kMh, 2.0)) /
+                        (dbase * std::pow(tbase, 3.0));
   const double unit_of[3] = {u_k, u_k3, u_cool};
 
   const double lnT0 = std::log(chem->TemperatureStart);

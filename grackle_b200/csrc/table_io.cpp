@@ -54,7 +54,7 @@ int gr_load_cloudy_table(chemistry_data *chem, chemistry_data_storage *rates, cl
   const double aprod = units->a_value * units->a_units;
   const double tbase1 = units->time_units;
   const double xbase1 = co_len / aprod;
-  const double dbase1 = co_den * std::pow(aprod, 3);
+  const double dbase1 = co_den * std::pow(aprod, 3.0);
   const double mh = 1.67e-24;
   const double cool_unit = (std::pow(units->a_units, 5) * std::pow(xbase1, 2) * std::pow(mh, 2)) /
                            (std::pow(tbase1, 3) * dbase1);

@@ -122,6 +122,9 @@ double grb200_last_kernel_ms(chemistry_data_storage *my_rates);
 /* number of kernel launches issued by the library since load (bench gpu_launches) */
 long long grb200_kernel_launch_count(void);
 
+/* measured non-tensor FP64 FMA throughput of the current device [TFLOP/s] (microbenchmark) */
+double grb200_measure_fp64_tflops(void);
+
 /* 1 if a CUDA device is usable, else 0 (never falls back to the CPU) */
 int grb200_device_available(void);
 

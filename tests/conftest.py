@@ -1,0 +1,30 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def oracle_lib():
+    from grackle_b200 import capi
+    return capi.load_oracle()
+
+
+@pytest.fixture(scope="session")
+def product_lib():
+    from grackle_b200 import capi
+    return capi.load_product()
+
+
+@pytest.fixture(scope="session")
+def synth_table():
+    from grackle_b200 import synth_tables
+    return synth_tables.ensure()
