@@ -189,6 +189,8 @@ def load_oracle():
     lib.oracle_inject_uvb.restype = None
     lib.oracle_clear_injected.restype = None
     lib.oracle_last_subcycles_sum.restype = C.c_longlong
+    lib.oracle_set_roundoff_noise.argtypes = [C.c_double, C.c_ulonglong]
+    lib.oracle_set_roundoff_noise.restype = None
     lib.oracle_last_subcycles_max.restype = C.c_longlong
     return lib
 

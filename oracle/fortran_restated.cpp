@@ -1387,6 +1387,21 @@ void make_consistent_g(const FArgs &a)
 // diagnostics shared with the test harness (not part of the reference)
 long long g_subcycles_sum = 0, g_subcycles_max = 0;
 
+// Conditioning probe (test harness only, OFF by default => bit-exact reference algorithm):
+// multiply edot by (1 + amp*u), u in [-1,1] hashed from (cell, iter, seed), in every
+// subcycle.  Running the oracle against itself with amp ~ 1e-15 tells which cells' answers
+// are reproducible under round-off-level changes and which are chaotic (limit cycles).
+double g_noise_amp = 0.0;
+unsigned long long g_noise_seed = 0;
+inline double noise_unit(unsigned long long a, unsigned long long b, unsigned long long c)
+{
+  unsigned long long z = a * 0x9E3779B97F4A7C15ull + b * 0xBF58476D1CE4E5B9ull + c * 0x94D049BB133111EBull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (double)(z >> 11) * (2.0 / 9007199254740992.0) - 1.0;
+}
+
 void solve_rate_cool(const FArgs &a, int *ierr)
 {
   const double tolerance = 1.0e-10;
@@ -1437,6 +1452,9 @@ void solve_rate_cool(const FArgs &a, int *ierr)
       for (int i = is; i <= ie; i++) if (r.itmask[i]) { r.dtit[i] = huge8; sub_sum++; }
 
       cool1d_multi_g(a, r, j, k, iter, comp1, comp2);
+      if (g_noise_amp != 0.0)
+        for (int i = is; i <= ie; i++) if (r.itmask[i])
+          r.edot[i] *= 1.0 + g_noise_amp * noise_unit(IDX(a, i, j, k), (unsigned long long)iter, g_noise_seed);
 
       if (a.ispecies > 0) {
         lookup_cool_rates1d_g(a, r, j, k, anydust, dom, coolunit, tbase1, xbase1, dx_cgs, c_ljeans);
@@ -1546,6 +1564,7 @@ void solve_rate_cool(const FArgs &a, int *ierr)
 // ==========================================================================
 extern "C" {
 
+void oracle_set_roundoff_noise(double amp, unsigned long long seed) { g_noise_amp = amp; g_noise_seed = seed; }
 long long oracle_last_subcycles_sum(void) { return g_subcycles_sum; }
 long long oracle_last_subcycles_max(void) { return g_subcycles_max; }
 
