@@ -33,7 +33,10 @@ inline double series(double x, const double (&c)[N])
 {
   double s = c[0];
   if (N > 1) s += c[1] * x;
-  for (int n = 2; n < N; ++n) s += c[n] * std::pow(x, (double)n);
+  // pow(x, 2) with a literal 2 is folded to x*x by gcc (the compiler the reference and the
+  // oracle are built with); glibc's pow(x, 2.0) is not always the correctly rounded square
+  if (N > 2) s += c[2] * (x * x);
+  for (int n = 3; n < N; ++n) s += c[n] * std::pow(x, (double)n);
   return s;
 }
 

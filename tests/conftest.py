@@ -28,3 +28,15 @@ def product_lib():
 def synth_table():
     from grackle_b200 import synth_tables
     return synth_tables.ensure()
+
+
+@pytest.fixture(scope="session")
+def metal_table_2008():
+    """cloudy_metals_2008_3D.h5 (old-style rank-3 table the freefall_metal golden run used):
+    a copy under tests/golden/ travels to the GPU box; the reference checkout is the
+    source in the dev container"""
+    for p in (os.path.join(ROOT, "tests", "golden", "cloudy_metals_2008_3D.h5"),
+              "/root/reference/grackle_data_files/input/cloudy_metals_2008_3D.h5"):
+        if os.path.exists(p):
+            return p
+    pytest.skip("cloudy_metals_2008_3D.h5 not available")
