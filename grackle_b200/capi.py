@@ -19,7 +19,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(_HERE)
-PRODUCT_SO = os.path.join(_HERE, "lib", "libgrackle_b200.so")
+# GRB200_LIB selects another BUILD of the same CUDA library (tuning experiments); never a fallback
+PRODUCT_SO = os.environ.get("GRB200_LIB") or os.path.join(_HERE, "lib", "libgrackle_b200.so")
 ORACLE_SO = os.path.join(REPO, "oracle", "_ref", "libgrackle_oracle.so")
 
 c_dp = C.POINTER(C.c_double)

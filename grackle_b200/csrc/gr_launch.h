@@ -4,7 +4,12 @@
 #include <cuda_runtime.h>
 #include "gr_device.h"
 
+#ifndef GRB_SOLVE_THREADS
 #define GRB_SOLVE_THREADS 128
+#endif
+#ifndef GRB_SOLVE_MINBLOCKS
+#define GRB_SOLVE_MINBLOCKS 1     /* resident CTAs per SM the register allocator must allow */
+#endif
 
 void grb_launch_thermo(const GrParams &P, int mode, cudaStream_t st);     // 0 p, 1 T, 2 gamma
 void grb_launch_fill(const GrParams &P, double value, cudaStream_t st);

@@ -340,7 +340,7 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 }
 
 template <int PC>
-__global__ void __launch_bounds__(GRB_SOLVE_THREADS, 1) k_solve(const __grid_constant__ GrParams P)
+__global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P)
 {
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
