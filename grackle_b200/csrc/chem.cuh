@@ -31,7 +31,7 @@ __device__ __forceinline__ double lerp_row(const double *row, int ncol, int col,
 // Rahmati+13 eq. 13/14 shielding fraction (cool1d_multi_g.F:788-792, solve_rate_cool_g.F:1518-1520)
 __device__ __forceinline__ double rahmati_f(double nratio)
 {
-  return 0.98 * pow(1.0 + pow(nratio, 1.64), -2.28) + 0.02 * pow(1.0 + nratio, -0.84);
+  return 0.98 * pow_pos(1.0 + pow_pos(nratio, 1.64), -2.28) + 0.02 * pow_pos(1.0 + nratio, -0.84);
 }
 
 struct TIndex { int idx; double t1, t2, tdef; };   // idx is 1-based like the Fortran
@@ -139,7 +139,7 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
     const double gaHp = COOL_LERP(L_GAHP), gael = COOL_LERP(L_GAEL), h2lte = COOL_LERP(L_H2LTE);
     double fudge = 1.0;
     if (P.ih2optical == 1) {
-      fudge = pow(0.76 * c.d * dom / 8.e9, -0.45);
+      fudge = pow_pos(0.76 * c.d * dom / 8.e9, -0.45);
       fudge = dmin(fudge, 1.0);
     }
     const double galdl = gaHI * c.HI + gaH2 * c.H2I / 2.0 + gaHe * c.HeI / 4.0 + gaHp * c.HII + gael * c.de;
@@ -147,10 +147,10 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
     edot = edot - (double)P.ih2co * fudge * c.H2I * h2lte / (1.0 + gphdl1 / galdl) / (2.0 * dom);
     if (P.iciecool == 1 && c.d * dom > 1e10) {
       const double cieco = COOL_LERP(L_CIECO);
-      double tau = pow((c.d / 2e16) * dom, 2.8);
+      double tau = pow_pos((c.d / 2e16) * dom, 2.8);
       tau = dmax(tau, 1.e-5);
       double ciefudge = dmin((1.0 - exp(-tau)) / tau, 1.0);
-      tau = pow((c.d / 2.e18) * dom, 8.0);
+      tau = pow_pos((c.d / 2.e18) * dom, 8.0);
       tau = dmax(tau, 1.e-5);
       ciefudge = ciefudge * dmin((1.0 - exp(-tau)) / tau, 1.0);
       edot = ciefudge * (edot - c.H2I * (c.d * cieco));
@@ -181,11 +181,11 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   if (PC > 0) {     // UVB photo-heating with optional self-shielding (:758-913)
     double fH = 1.0, fHe = 1.0;
     if (P.iradshield >= 1 && !(P.k24 < GRB_TINY8)) {
-      const double nSSh = P.ssh_sig_hi * pow(th.tgas / 1.0e4, 0.17) * P.ssh_k24;
+      const double nSSh = P.ssh_sig_hi * pow_pos(th.tgas / 1.0e4, 0.17) * P.ssh_k24;
       fH = rahmati_f((c.HI + c.HII) * dom / nSSh);
     }
     if (P.iradshield >= 2 && !(P.k26 < GRB_TINY8)) {
-      const double nSSh_he = P.ssh_sig_hei * pow(th.tgas / 1.0e4, 0.17) * P.ssh_k26;
+      const double nSSh_he = P.ssh_sig_hei * pow_pos(th.tgas / 1.0e4, 0.17) * P.ssh_k26;
       fHe = rahmati_f(0.25 * (c.HeI + c.HeII + c.HeIII) * dom / nSSh_he);
     }
     const double ip = (double)P.ipiht;
@@ -215,8 +215,8 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
       geff = (th.tgas > 2.e4) ? 0.0 : P.gammaha * 0.05 * myisrf;
     } else {
       const double pe_X = myisrf * dom_inv * sqrt(th.tgas) / th.myde;
-      const double pe_eps = (4.9e-2 / (1.0 + pow(pe_X / 1925.0, 0.73))) +
-                            ((3.7e-2 * pow(th.tgas / 1.e4, 0.7)) / (1.0 + (pe_X / 5000.0)));
+      const double pe_eps = (4.9e-2 / (1.0 + pow_pos(pe_X / 1925.0, 0.73))) +
+                            ((3.7e-2 * pow_pos(th.tgas / 1.e4, 0.7)) / (1.0 + (pe_X / 5000.0)));
       geff = P.gammaha * pe_eps * myisrf;
     }
     edot = edot + geff * th.rhoH * dom_inv * th.dust2gas / P.fgr;
@@ -224,8 +224,8 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
 
   if ((P.idustall > 0) || (P.idustrec > 0)) {   // grain recombination cooling (:1005-1023)
     const double regr = COOL_LERP(L_REGR);
-    const double grbeta = 0.74 / pow(th.tgas, 0.068);
-    edot = edot - regr * pow(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
+    const double grbeta = 0.74 / pow_pos(th.tgas, 0.068);
+    edot = edot - regr * pow_pos(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
   }
 
   // Compton + X-ray Compton (:1027-1041)

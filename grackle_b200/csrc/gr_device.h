@@ -82,6 +82,7 @@ struct GrParams {
   double avgsighi, avgsighei, avgsigheii;
   // derived once per call on the host (solve_rate_cool_g.F:331-343, cool1d_multi_g.F:179-198)
   double dom, dom_inv, tbase1, xbase1, dbase1, coolunit, uvel, chunit, dx_cgs, c_ljeans;
+  double log10_tcmb;                 // log10(comp2), cell-invariant (cool1d_cloudy_g.F:110)
   double zr, comp1, comp2, logtem0, logtem9, dlogtem, d_logtem0, d_logtem9, d_dlogtem;
   double a3, a3inv;                  // comoving <-> proper factors (aye^3, aye^-3)
   // Rahmati+13 cell-invariant factors: 6.73e-3*(sig/2.49e-18)^(-2/3) and (k/tbase1/1e-12)^(2/3)

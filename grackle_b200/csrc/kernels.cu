@@ -224,37 +224,40 @@ struct SubState {           // per-cell carry between subcycles
   int iter;
 };
 
-// one subcycle of solve_rate_cool_g.F:451-817 for one cell; returns true when the cell
-// has reached dt
+// One subcycle of solve_rate_cool_g.F:451-817 for one cell, in three stages so that the
+// warps of a CTA can be re-aligned between them (see k_solve): (a) cool_rate, (b) the rate
+// lookup, (c) rate-limited dt, energy update and the species sweep.  subcycle_finish returns
+// true when the cell has reached dt.
 template <int PC>
-__device__ __forceinline__ bool subcycle(const GrParams &P, Cell &c, SubState &s, size_t x,
-                                         int ci, int cj, int ck)
+__device__ __forceinline__ void subcycle_lookup(const GrParams &P, const Cell &c, const Thermo &th, size_t x, const Rates &r)
+{
+  Neigh nb;
+  if (PC > 1 && P.iH2shield == 1) {
+    const double sc = (P.iexpand == 1) ? P.a3inv : 1.0;
+    const size_t sj = (size_t)P.in, sk = (size_t)P.in * P.jn;
+    const double *D = P.f[F_D];
+    nb.d[0] = D[x + 1] * sc; nb.d[1] = D[x - 1] * sc; nb.d[2] = D[x + sj] * sc;
+    nb.d[3] = D[x - sj] * sc; nb.d[4] = D[x + sk] * sc; nb.d[5] = D[x - sk] * sc;
+  }
+  lookup_rates<PC>(P, c, th, nb, r);
+}
+
+template <int PC>
+__device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubState &s, const Thermo &th,
+                                                const Rates &r)
 {
   const double dt = P.dt;
   double dtit = GRB_HUGE8;
-  Thermo th;
-  cool_rate<PC>(P, c, s.iter == 1, s.tgasold, th);
   double edot = th.edot;
 
-  Rates r;
   if (PC > 0) {
-    Neigh nb;
-    if (PC > 1 && P.iH2shield == 1) {
-      const double sc = (P.iexpand == 1) ? P.a3inv : 1.0;
-      const size_t sj = (size_t)P.in, sk = (size_t)P.in * P.jn;
-      const double *D = P.f[F_D];
-      nb.d[0] = D[x + 1] * sc; nb.d[1] = D[x - 1] * sc; nb.d[2] = D[x + sj] * sc;
-      nb.d[3] = D[x - sj] * sc; nb.d[4] = D[x + sk] * sc; nb.d[5] = D[x - sk] * sc;
-      (void)ci; (void)cj; (void)ck;
-    }
-    lookup_rates<PC>(P, c, th, nb, r);
     double dedot, HIdot;
     rate_derivs<PC>(P, c, th, r, dedot, HIdot, edot);
 
     // solve_rate_cool_g.F:554-646
     if (fabs(dedot) < GRB_TINY8) dedot = dmin(GRB_TINY, c.de);
     if (fabs(HIdot) < GRB_TINY8) HIdot = dmin(GRB_TINY, c.HI);
-    if (dmin(fabs(r.k1 * c.de * c.HI), fabs(r.k2 * c.HII * c.de)) / dmax(fabs(dedot), fabs(HIdot)) > 1.0e6) {
+    if (dmin(fabs(RK(k1) * c.de * c.HI), fabs(RK(k2) * c.HII * c.de)) / dmax(fabs(dedot), fabs(HIdot)) > 1.0e6) {
       dedot = GRB_TINY8;
       HIdot = GRB_TINY8;
     }
@@ -267,20 +270,21 @@ __device__ __forceinline__ bool subcycle(const GrParams &P, Cell &c, SubState &s
     if (PC > 1 && c.d * P.dom > 1e8 && edot > 0.0) {
       // keep the 3-body equilibrium H abundance from changing by more than 10 %
       const double fd = P.fh * c.d;
-      const double k22lo = ld(P.k22a + r.idx - 1), k22hi = ld(P.k22a + r.idx);
-      const double k13lo = ld(P.k13a + r.idx - 1), k13hi = ld(P.k13a + r.idx);
-      const double eqt2 = dmin(log(th.tgas) + 0.1 * P.dlogtem, r.t2);
-      double eqtdef = (eqt2 - r.t1) / (r.t2 - r.t1);
+      const int ridx = (int)RK(idx);
+      const double k22lo = ld(P.k22a + ridx - 1), k22hi = ld(P.k22a + ridx);
+      const double k13lo = ld(P.k13a + ridx - 1), k13hi = ld(P.k13a + ridx);
+      const double eqt2 = dmin(log(th.tgas) + 0.1 * P.dlogtem, RK(t2));
+      double eqtdef = (eqt2 - RK(t1)) / (RK(t2) - RK(t1));
       const double eqk222 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk132 = k13lo + (k13hi - k13lo) * eqtdef;
       const double heq2 = (-1.0 / (4.0 * eqk222)) * (eqk132 - sqrt(8.0 * eqk132 * eqk222 * fd + eqk132 * eqk132));
-      const double eqt1 = dmax(log(th.tgas) - 0.1 * P.dlogtem, r.t1);
-      eqtdef = (eqt1 - r.t1) / (r.t2 - r.t1);
+      const double eqt1 = dmax(log(th.tgas) - 0.1 * P.dlogtem, RK(t1));
+      eqtdef = (eqt1 - RK(t1)) / (RK(t2) - RK(t1));
       const double eqk221 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk131 = k13lo + (k13hi - k13lo) * eqtdef;
       const double heq1 = (-1.0 / (4.0 * eqk221)) * (eqk131 - sqrt(8.0 * eqk131 * eqk221 * fd + eqk131 * eqk131));
       const double dheq = (fabs(heq2 - heq1) / (exp(eqt2) - exp(eqt1))) * (th.tgas / th.p2d) * edot;
-      const double heq = (-1.0 / (4.0 * r.k22)) * (r.k13 - sqrt(8.0 * r.k13 * r.k22 * fd + r.k13 * r.k13));
+      const double heq = (-1.0 / (4.0 * RK(k22))) * (RK(k13) - sqrt(8.0 * RK(k13) * RK(k22) * fd + RK(k13) * RK(k13)));
       dtit = dmin(dtit, 0.1 * heq / dheq);
     }
     // (the reference's iter>10 rule min(1.5*olddtit, dtit) is inert: olddtit is always huge8)
@@ -339,15 +343,30 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
   if (PC > 2) { P.f[F_DI][x] = c.DI; P.f[F_DII][x] = c.DII; P.f[F_HDI][x] = c.HDI; }
 }
 
+// CTA-wide re-alignment points.  The executed path of one subcycle is ~100 KB of SASS,
+// three times the SM's 32 KB instruction cache; warps that drift apart each stream it from
+// L2 on their own (ncu round 1: 55 % of all stall cycles were stall_no_inst).  Barriers
+// between the stages keep the warps of a CTA inside the same few KB of code, so one warp's
+// fetch serves all of them.
+#ifndef GRB_LOCKSTEP
+#define GRB_LOCKSTEP 1
+#endif
+#if GRB_LOCKSTEP
+#define GRB_ALIGN() __syncthreads()
+#else
+#define GRB_ALIGN() ((void)0)
+#endif
+
 template <int PC>
 __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P)
 {
+  extern __shared__ double rate_slots[];     // [NRATES][GRB_SOLVE_THREADS]
+  const Rates r{rate_slots + threadIdx.x};
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   Cell c;
   SubState s;
   size_t x = 0;
-  int ci = 0, cj = 0, ck = 0;
   bool active = false, exhausted = false;
   unsigned long long my_sub = 0, my_max = 0, my_itmax = 0, my_nan = 0;
 
@@ -362,6 +381,7 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
       if (!active && !exhausted) {
         const long long t = (long long)(base + __popc(need & ((1u << lane) - 1)));
         if (t < P.nactive) {
+          int ci, cj, ck;
           x = cell_index(P, t, ci, cj, ck);
           bool run = true;
           if (P.iradtrans == 1 && P.iradcoupled == 1) {   // coupled-RT masks (:418-439)
@@ -377,14 +397,28 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
         }
       }
     }
+    // after the refill every lane either owns a cell or has seen the end of the queue
+#if GRB_LOCKSTEP
+    if (__syncthreads_or(active ? 1 : 0) == 0) break;
+#else
     if (__ballot_sync(full, active) == 0) {
       if (__ballot_sync(full, !exhausted) == 0) break;
       continue;
     }
+#endif
     // ---- one subcycle on every busy lane ----
+    Thermo th;
     if (active) {
       load_extras<PC>(P, x, c);
-      const bool done = subcycle<PC>(P, c, s, x, ci, cj, ck);
+      cool_rate<PC>(P, c, s.iter == 1, s.tgasold, th);
+    }
+    GRB_ALIGN();
+    if (PC > 0) {
+      if (active) subcycle_lookup<PC>(P, c, th, x, r);
+      GRB_ALIGN();
+    }
+    if (active) {
+      const bool done = subcycle_finish<PC>(P, c, s, th, r);
       my_sub++;
       if (done || s.iter >= P.itmax) {
         if (!done) my_itmax++;
@@ -437,6 +471,7 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double *sink, int iters, doub
 // ------------------------------------------------------------------------------
 // host-callable launchers (declared in gr_launch.h)
 // ------------------------------------------------------------------------------
+#define GRB_SOLVE_SMEM ((size_t)NRATES * GRB_SOLVE_THREADS * sizeof(double))
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 }  // namespace grb
@@ -492,7 +527,9 @@ void grb_launch_dust_temperature(const GrParams &P, cudaStream_t st)
 // the SM count); P.work_counter must be zero
 void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
 {
-#define CALL(PCV) k_solve<PCV><<<blocks, GRB_SOLVE_THREADS, 0, st>>>(P);
+#define CALL(PCV)                                                                                  \
+  cudaFuncSetAttribute(k_solve<PCV>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM); \
+  k_solve<PCV><<<blocks, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM, st>>>(P);
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
 }
@@ -500,7 +537,9 @@ void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
 int grb_solve_max_blocks_per_sm(int pc)
 {
   int n = 0;
-#define CALL(PCV) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV>, GRB_SOLVE_THREADS, 0);
+#define CALL(PCV)                                                                                  \
+  cudaFuncSetAttribute(k_solve<PCV>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM); \
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV>, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM);
   DISPATCH_PC(pc, CALL)
 #undef CALL
   return n;

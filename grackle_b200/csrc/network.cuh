@@ -4,20 +4,63 @@
 #define GRB200_NETWORK_CUH
 
 #include "chem.cuh"
+#include "gr_launch.h"
 
 namespace grb {
 
-struct Rates {
-  double k1, k2, k3, k4, k5, k6, k57, k58;
-  double k7, k8, k9, k10, k11, k12, k13, k14, k15, k16, k17, k18, k19, k22;
-  double ncrn, ncrd1, ncrd2;
-  double k50, k51, k52, k53, k54, k55, k56;
-  double h2dust;
-  double k24s, k25s, k26s, k28s, k29s, k30s, k31s;   // (self-)shielded photo rates
-  // log-T bracket of this lookup, needed by the H-equilibrium dt limiter
-  int idx;
-  double t1, t2;
+// The rates of one cell-subcycle live in SHARED memory between the lookup and the species
+// update (slot-major: slot i of thread t at base[i*GRB_SOLVE_THREADS + t], conflict-free),
+// which takes ~90 registers off the solve kernel.  Rates is a view of one thread's column.
+enum {
+  RI_k1,
+  RI_k2,
+  RI_k3,
+  RI_k4,
+  RI_k5,
+  RI_k6,
+  RI_k57,
+  RI_k58,
+  RI_k7,
+  RI_k8,
+  RI_k9,
+  RI_k10,
+  RI_k11,
+  RI_k12,
+  RI_k13,
+  RI_k14,
+  RI_k15,
+  RI_k16,
+  RI_k17,
+  RI_k18,
+  RI_k19,
+  RI_k22,
+  RI_ncrn,
+  RI_ncrd1,
+  RI_ncrd2,
+  RI_k50,
+  RI_k51,
+  RI_k52,
+  RI_k53,
+  RI_k54,
+  RI_k55,
+  RI_k56,
+  RI_h2dust,
+  RI_k24s,
+  RI_k25s,
+  RI_k26s,
+  RI_k28s,
+  RI_k29s,
+  RI_k30s,
+  RI_k31s,
+  RI_t1,
+  RI_t2,
+  RI_idx,          // log-T bin of the lookup (stored as a double)
+  NRATES
 };
+struct Rates {
+  double *base;    // shared memory, already offset by threadIdx.x
+};
+#define RK(name) (r.base[RI_##name * GRB_SOLVE_THREADS])
 
 // neighbour densities for the Sobolev-like H2 shielding length (H2_self_shielding == 1)
 struct Neigh { double d[6]; };
@@ -27,7 +70,7 @@ struct Neigh { double d[6]; };
 // ---------------------------------------------------------------------------------
 template <int PC>
 __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Thermo &th,
-                                    const Neigh &nb, Rates &r)
+                                    const Neigh &nb, const Rates &r)
 {
   const bool anydust = (P.idust > 0) || (P.idustall > 0);
   const double dom = P.dom;
@@ -35,31 +78,31 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
   const TIndex ti = t_index(P, logtem);
-  r.idx = ti.idx; r.t1 = ti.t1; r.t2 = ti.t2;
+  RK(idx) = (double)ti.idx; RK(t1) = ti.t1; RK(t2) = ti.t2;
   const double tdef = ti.tdef;
   const double *row = P.chem + (size_t)(ti.idx - 1) * NCHEM;
 #define K_LERP(col) lerp_row(row, NCHEM, col, tdef)
 
-  r.k1 = K_LERP(C_K1); r.k2 = K_LERP(C_K2); r.k3 = K_LERP(C_K3); r.k4 = K_LERP(C_K4);
-  r.k5 = K_LERP(C_K5); r.k6 = K_LERP(C_K6); r.k57 = K_LERP(C_K57); r.k58 = K_LERP(C_K58);
+  RK(k1) = K_LERP(C_K1); RK(k2) = K_LERP(C_K2); RK(k3) = K_LERP(C_K3); RK(k4) = K_LERP(C_K4);
+  RK(k5) = K_LERP(C_K5); RK(k6) = K_LERP(C_K6); RK(k57) = K_LERP(C_K57); RK(k58) = K_LERP(C_K58);
 
   if (PC > 1) {
-    r.k7 = K_LERP(C_K7); r.k8 = K_LERP(C_K8); r.k9 = K_LERP(C_K9); r.k10 = K_LERP(C_K10);
-    r.k11 = K_LERP(C_K11); r.k12 = K_LERP(C_K12); r.k13 = K_LERP(C_K13); r.k14 = K_LERP(C_K14);
-    r.k15 = K_LERP(C_K15); r.k16 = K_LERP(C_K16); r.k17 = K_LERP(C_K17); r.k18 = K_LERP(C_K18);
-    r.k19 = K_LERP(C_K19); r.k22 = K_LERP(C_K22);
-    r.ncrn = K_LERP(C_NCRN); r.ncrd1 = K_LERP(C_NCRD1); r.ncrd2 = K_LERP(C_NCRD2);
+    RK(k7) = K_LERP(C_K7); RK(k8) = K_LERP(C_K8); RK(k9) = K_LERP(C_K9); RK(k10) = K_LERP(C_K10);
+    RK(k11) = K_LERP(C_K11); RK(k12) = K_LERP(C_K12); RK(k13) = K_LERP(C_K13); RK(k14) = K_LERP(C_K14);
+    RK(k15) = K_LERP(C_K15); RK(k16) = K_LERP(C_K16); RK(k17) = K_LERP(C_K17); RK(k18) = K_LERP(C_K18);
+    RK(k19) = K_LERP(C_K19); RK(k22) = K_LERP(C_K22);
+    RK(ncrn) = K_LERP(C_NCRN); RK(ncrd1) = K_LERP(C_NCRD1); RK(ncrd2) = K_LERP(C_NCRD2);
   }
   if (PC > 2) {
-    r.k50 = K_LERP(C_K50); r.k51 = K_LERP(C_K51); r.k52 = K_LERP(C_K52); r.k53 = K_LERP(C_K53);
-    r.k54 = K_LERP(C_K54); r.k55 = K_LERP(C_K55); r.k56 = K_LERP(C_K56);
+    RK(k50) = K_LERP(C_K50); RK(k51) = K_LERP(C_K51); RK(k52) = K_LERP(C_K52); RK(k53) = K_LERP(C_K53);
+    RK(k54) = K_LERP(C_K54); RK(k55) = K_LERP(C_K55); RK(k56) = K_LERP(C_K56);
   }
 
   // H2 formation on grains: bilinear in (ln T, ln T_dust) (:1327-1378)
-  r.h2dust = 0.0;
+  RK(h2dust) = 0.0;
   if (anydust) {
     if (th.tdust > P.dtemend) {
-      r.h2dust = GRB_TINY8;
+      RK(h2dust) = GRB_TINY8;
     } else {
       double dl = log(th.tdust);
       dl = dmax(dl, P.d_logtem0);
@@ -72,16 +115,16 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
       const double *c2 = c1 + P.nratec;
       const double dusti1 = ld(c1) + (ld(c1 + 1) - ld(c1)) * tdef;
       const double dusti2 = ld(c2) + (ld(c2 + 1) - ld(c2)) * tdef;
-      r.h2dust = dusti1 + (dusti2 - dusti1) * d_tdef;
-      r.h2dust = r.h2dust * th.dust2gas;
+      RK(h2dust) = dusti1 + (dusti2 - dusti1) * d_tdef;
+      RK(h2dust) = RK(h2dust) * th.dust2gas;
     }
   }
 
-  r.k24s = P.k24; r.k25s = P.k25; r.k26s = P.k26; r.k28s = P.k28; r.k29s = P.k29; r.k30s = P.k30;
-  r.k31s = 0.0;
+  RK(k24s) = P.k24; RK(k25s) = P.k25; RK(k26s) = P.k26; RK(k28s) = P.k28; RK(k29s) = P.k29; RK(k30s) = P.k30;
+  RK(k31s) = 0.0;
 
   if (PC > 1) {     // H2 self-shielding, Wolcott-Green & Haiman (2019) (:1397-1490)
-    r.k31s = (P.iradtrans == 0) ? P.k31 : P.k31 + c.kdissH2I;
+    RK(k31s) = (P.iradtrans == 0) ? P.k31 : P.k31 + c.kdissH2I;
     if (P.iH2shield > 0) {
       double l_H2shield;
       if (P.iH2shield == 1) {
@@ -108,16 +151,16 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
                          (-0.9639 * log10(tuse) + 3.892);
       const double x = 2.0e-15 * N_H2;
       const double b_doppler = 1e-5 * sqrt(2.0 * GRB_KBOLTZ * th.tgas / GRB_MASS_H);
-      double f_shield = 0.965 / pow(1.0 + x / b_doppler, aWG) +
+      double f_shield = 0.965 / pow_pos(1.0 + x / b_doppler, aWG) +
                         0.035 * exp(-8.5e-4 * sqrt(1.0 + x)) / sqrt(1.0 + x);
       f_shield = dmin(f_shield, 1.0);
-      r.k31s = f_shield * r.k31s;
+      RK(k31s) = f_shield * RK(k31s);
     }
-    if (P.iH2shieldcustom > 0) r.k31s = c.fshield * r.k31s;
+    if (P.iH2shieldcustom > 0) RK(k31s) = c.fshield * RK(k31s);
   }
 
   if (P.iradshield > 0) {   // UVB self-shielding (:1492-1676)
-    const double tfac = pow(th.tgas / 1.0e4, 0.17);
+    const double tfac = pow_pos(th.tgas / 1.0e4, 0.17);
     double nratio = (c.HI + c.HII);
     if (PC > 1) {
       nratio = nratio + c.HM + c.H2I + c.H2II;
@@ -127,33 +170,33 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
     const double fH = rahmati_f(nratio);
     nratio = 0.25 * (c.HeI + c.HeII + c.HeIII) * dom / (P.ssh_sig_hei * tfac * P.ssh_k26);
     const double fHe = rahmati_f(nratio);
-    r.k24s = (P.k24 < GRB_TINY8) ? 0.0 : r.k24s * fH;
-    r.k29s = (P.k29 < GRB_TINY8) ? 0.0 : r.k29s * fH;
+    RK(k24s) = (P.k24 < GRB_TINY8) ? 0.0 : RK(k24s) * fH;
+    RK(k29s) = (P.k29 < GRB_TINY8) ? 0.0 : RK(k29s) * fH;
     if (P.iradshield == 1) {
-      r.k25s = P.k25; r.k26s = P.k26;
+      RK(k25s) = P.k25; RK(k26s) = P.k26;
     } else if (P.iradshield == 2 || P.iradshield == 3) {
-      r.k26s = (P.k26 < GRB_TINY8) ? 0.0 : r.k26s * fHe;
-      r.k28s = (P.k28 < GRB_TINY8) ? 0.0 : r.k28s * fHe;
-      r.k30s = (P.k30 < GRB_TINY8) ? 0.0 : r.k30s * fHe;
-      r.k25s = (P.iradshield == 2) ? P.k25 : 0.0;
+      RK(k26s) = (P.k26 < GRB_TINY8) ? 0.0 : RK(k26s) * fHe;
+      RK(k28s) = (P.k28 < GRB_TINY8) ? 0.0 : RK(k28s) * fHe;
+      RK(k30s) = (P.k30 < GRB_TINY8) ? 0.0 : RK(k30s) * fHe;
+      RK(k25s) = (P.iradshield == 2) ? P.k25 : 0.0;
     }
   }
 
   // density-dependent collisional dissociation of H2 (Martin+96) (:1709-1733)
   if (PC > 1 && P.ithreebody == 0) {
     const double nh = dmin(c.HI * dom, 1.0e9);
-    r.k13 = GRB_TINY8;
+    RK(k13) = GRB_TINY8;
     if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
       double dd[14];
 #pragma unroll
       for (int n = 0; n < 14; n++) dd[n] = K_LERP(C_K13DD0 + n);
-      double cid = dd[0] - dd[1] / (1.0 + pow(nh / dd[4], dd[6])) + dd[2] -
-                   dd[3] / (1.0 + pow(nh / dd[5], dd[6]));
-      cid = dmax(pow(10.0, cid), GRB_TINY8);
-      double dtn = dd[7] - dd[8] / (1.0 + pow(nh / dd[11], dd[13])) + dd[9] -
-                   dd[10] / (1.0 + pow(nh / dd[12], dd[13]));
-      dtn = dmax(pow(10.0, dtn), GRB_TINY8);
-      r.k13 = dtn + cid;
+      double cid = dd[0] - dd[1] / (1.0 + pow_pos(nh / dd[4], dd[6])) + dd[2] -
+                   dd[3] / (1.0 + pow_pos(nh / dd[5], dd[6]));
+      cid = dmax(exp10(cid), GRB_TINY8);
+      double dtn = dd[7] - dd[8] / (1.0 + pow_pos(nh / dd[11], dd[13])) + dd[9] -
+                   dd[10] / (1.0 + pow_pos(nh / dd[12], dd[13]));
+      dtn = dmax(exp10(dtn), GRB_TINY8);
+      RK(k13) = dtn + cid;
     }
   }
 #undef K_LERP
@@ -170,35 +213,35 @@ __device__ inline void rate_derivs(const GrParams &P, const Cell &c, const Therm
   const bool anydust = (P.idust > 0) || (P.idustall > 0);
   const double de = c.de, HI = c.HI, HII = c.HII, HeI = c.HeI, HeII = c.HeII, HeIII = c.HeIII;
   if (PC == 1) {
-    dedot = + r.k1 * HI * de + r.k3 * HeI * de / 4.0 + r.k5 * HeII * de / 4.0
-            - r.k2 * HII * de - r.k4 * HeII * de / 4.0 - r.k6 * HeIII * de / 4.0
-            + r.k57 * HI * HI + r.k58 * HI * HeI / 4.0
-            + (r.k24s * HI + r.k25s * HeII / 4.0 + r.k26s * HeI / 4.0);
-    HIdot = - r.k1 * HI * de + r.k2 * HII * de - r.k57 * HI * HI - r.k58 * HI * HeI / 4.0 - r.k24s * HI;
+    dedot = + RK(k1) * HI * de + RK(k3) * HeI * de / 4.0 + RK(k5) * HeII * de / 4.0
+            - RK(k2) * HII * de - RK(k4) * HeII * de / 4.0 - RK(k6) * HeIII * de / 4.0
+            + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0
+            + (RK(k24s) * HI + RK(k25s) * HeII / 4.0 + RK(k26s) * HeI / 4.0);
+    HIdot = - RK(k1) * HI * de + RK(k2) * HII * de - RK(k57) * HI * HI - RK(k58) * HI * HeI / 4.0 - RK(k24s) * HI;
   } else {
     const double HM = c.HM, H2I = c.H2I, H2II = c.H2II;
-    HIdot = - r.k1 * de * HI - r.k7 * de * HI - r.k8 * HM * HI - r.k9 * HII * HI
-            - r.k10 * H2II * HI / 2.0 - 2.0 * r.k22 * (HI * HI) * HI
-            + r.k2 * HII * de + 2.0 * r.k13 * HI * H2I / 2.0
-            + r.k11 * HII * H2I / 2.0 + 2.0 * r.k12 * de * H2I / 2.0
-            + r.k14 * HM * de + r.k15 * HM * HI + 2.0 * r.k16 * HM * HII
-            + 2.0 * r.k18 * H2II * de / 2.0 + r.k19 * H2II * HM / 2.0
-            - r.k57 * HI * HI - r.k58 * HI * HeI / 4.0 - r.k24s * HI
-            + 2.0 * r.k31s * H2I / 2.0;
-    if (anydust) HIdot = HIdot - 2.0 * r.h2dust * th.rhoH;
+    HIdot = - RK(k1) * de * HI - RK(k7) * de * HI - RK(k8) * HM * HI - RK(k9) * HII * HI
+            - RK(k10) * H2II * HI / 2.0 - 2.0 * RK(k22) * (HI * HI) * HI
+            + RK(k2) * HII * de + 2.0 * RK(k13) * HI * H2I / 2.0
+            + RK(k11) * HII * H2I / 2.0 + 2.0 * RK(k12) * de * H2I / 2.0
+            + RK(k14) * HM * de + RK(k15) * HM * HI + 2.0 * RK(k16) * HM * HII
+            + 2.0 * RK(k18) * H2II * de / 2.0 + RK(k19) * H2II * HM / 2.0
+            - RK(k57) * HI * HI - RK(k58) * HI * HeI / 4.0 - RK(k24s) * HI
+            + 2.0 * RK(k31s) * H2I / 2.0;
+    if (anydust) HIdot = HIdot - 2.0 * RK(h2dust) * th.rhoH;
 
-    dedot = + r.k1 * HI * de + r.k3 * HeI * de / 4.0 + r.k5 * HeII * de / 4.0
-            + r.k8 * HM * HI + r.k15 * HM * HI + r.k17 * HM * HII + r.k14 * HM * de
-            - r.k2 * HII * de - r.k4 * HeII * de / 4.0 - r.k6 * HeIII * de / 4.0
-            - r.k7 * HI * de - r.k18 * H2II * de / 2.0
-            + r.k57 * HI * HI + r.k58 * HI * HeI / 4.0
-            + (r.k24s * HI + r.k25s * HeII / 4.0 + r.k26s * HeI / 4.0);
+    dedot = + RK(k1) * HI * de + RK(k3) * HeI * de / 4.0 + RK(k5) * HeII * de / 4.0
+            + RK(k8) * HM * HI + RK(k15) * HM * HI + RK(k17) * HM * HII + RK(k14) * HM * de
+            - RK(k2) * HII * de - RK(k4) * HeII * de / 4.0 - RK(k6) * HeIII * de / 4.0
+            - RK(k7) * HI * de - RK(k18) * H2II * de / 2.0
+            + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0
+            + (RK(k24s) * HI + RK(k25s) * HeII / 4.0 + RK(k26s) * HeI / 4.0);
 
     // H2 formation heating, Omukai (2000) eq. 23
-    const double h2heatfac = 1.0 / (1.0 + (r.ncrn / (P.dom * (HI * r.ncrd1 + H2I * 0.5 * r.ncrd2))));
-    double H2delta = HI * (4.48 * r.k22 * (HI * HI) - 4.48 * r.k13 * H2I / 2.0);
+    const double h2heatfac = 1.0 / (1.0 + (RK(ncrn) / (P.dom * (HI * RK(ncrd1) + H2I * 0.5 * RK(ncrd2)))));
+    double H2delta = HI * (4.48 * RK(k22) * (HI * HI) - 4.48 * RK(k13) * H2I / 2.0);
     if (H2delta > 0.0) H2delta = H2delta * h2heatfac;
-    if (anydust) H2delta = H2delta + r.h2dust * HI * th.rhoH * (0.2 + 4.2 * h2heatfac);
+    if (anydust) H2delta = H2delta + RK(h2dust) * HI * th.rhoH * (0.2 + 4.2 * h2heatfac);
     edot = edot + P.chunit * H2delta * 1.0;
   }
   if (P.iradtrans == 1) {
@@ -229,91 +272,91 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
   double HIp = 0, HIIp = 0, dep = 0, HMp = 0, H2Ip = 0, H2IIp = 0, DIp = 0, DIIp = 0, HDIp = 0;
 
   if (PC == 1) {
-    scoef = r.k2 * HII * de;
-    acoef = r.k1 * de + r.k57 * HI + r.k58 * HeI / 4.0 + r.k24s;
+    scoef = RK(k2) * HII * de;
+    acoef = RK(k1) * de + RK(k57) * HI + RK(k58) * HeI / 4.0 + RK(k24s);
     if (rt) acoef = acoef + kphHI;
     HIp = (scoef * dt + HI) / (1.0 + acoef * dt);
 
-    scoef = r.k1 * HIp * de + r.k57 * HIp * HIp + r.k58 * HIp * HeI / 4.0 + r.k24s * HIp;
+    scoef = RK(k1) * HIp * de + RK(k57) * HIp * HIp + RK(k58) * HIp * HeI / 4.0 + RK(k24s) * HIp;
     if (rt) scoef = scoef + kphHI * HIp;
-    acoef = r.k2 * de;
+    acoef = RK(k2) * de;
     HIIp = (scoef * dt + HII) / (1.0 + acoef * dt);
     // (the reference also forms dep here and then discards it)
   }
 
   // helium, every network
-  scoef = r.k4 * HeII * de;
-  acoef = r.k3 * de + r.k26s;
+  scoef = RK(k4) * HeII * de;
+  acoef = RK(k3) * de + RK(k26s);
   if (rt_all) acoef = acoef + kphHeI;
   const double HeIp = (scoef * dt + HeI) / (1.0 + acoef * dt);
 
-  scoef = r.k3 * HeIp * de + r.k6 * HeIII * de + r.k26s * HeIp;
+  scoef = RK(k3) * HeIp * de + RK(k6) * HeIII * de + RK(k26s) * HeIp;
   if (rt_all) scoef = scoef + kphHeI * HeIp;
-  acoef = r.k4 * de + r.k5 * de + r.k25s;
+  acoef = RK(k4) * de + RK(k5) * de + RK(k25s);
   if (rt_all) acoef = acoef + kphHeII;
   const double HeIIp = (scoef * dt + HeII) / (1.0 + acoef * dt);
 
-  scoef = r.k5 * HeIIp * de + r.k25s * HeIIp;
+  scoef = RK(k5) * HeIIp * de + RK(k25s) * HeIIp;
   if (rt_all) scoef = scoef + kphHeII * HeIIp;
-  acoef = r.k6 * de;
+  acoef = RK(k6) * de;
   const double HeIIIp = (scoef * dt + HeIII) / (1.0 + acoef * dt);
 
   if (PC > 1) {
     const double HM = c.HM, H2I = c.H2I, H2II = c.H2II;
-    scoef = r.k2 * HII * de + 2.0 * r.k13 * HI * H2I / 2.0 + r.k11 * HII * H2I / 2.0 +
-            2.0 * r.k12 * de * H2I / 2.0 + r.k14 * HM * de + r.k15 * HM * HI +
-            2.0 * r.k16 * HM * HII + 2.0 * r.k18 * H2II * de / 2.0 + r.k19 * H2II * HM / 2.0 +
-            2.0 * r.k31s * H2I / 2.0;
-    acoef = r.k1 * de + r.k7 * de + r.k8 * HM + r.k9 * HII + r.k10 * H2II / 2.0 +
-            2.0 * r.k22 * (HI * HI) + r.k57 * HI + r.k58 * HeI / 4.0 + r.k24s;
+    scoef = RK(k2) * HII * de + 2.0 * RK(k13) * HI * H2I / 2.0 + RK(k11) * HII * H2I / 2.0 +
+            2.0 * RK(k12) * de * H2I / 2.0 + RK(k14) * HM * de + RK(k15) * HM * HI +
+            2.0 * RK(k16) * HM * HII + 2.0 * RK(k18) * H2II * de / 2.0 + RK(k19) * H2II * HM / 2.0 +
+            2.0 * RK(k31s) * H2I / 2.0;
+    acoef = RK(k1) * de + RK(k7) * de + RK(k8) * HM + RK(k9) * HII + RK(k10) * H2II / 2.0 +
+            2.0 * RK(k22) * (HI * HI) + RK(k57) * HI + RK(k58) * HeI / 4.0 + RK(k24s);
     if (rt) acoef = acoef + kphHI;
-    if (anydust) acoef = acoef + 2.0 * r.h2dust * th.rhoH;
+    if (anydust) acoef = acoef + 2.0 * RK(h2dust) * th.rhoH;
     HIp = (scoef * dt + HI) / (1. + acoef * dt);
 
-    scoef = r.k1 * HI * de + r.k10 * H2II * HI / 2.0 + r.k57 * HI * HI + r.k58 * HI * HeI / 4.0 +
-            r.k24s * HI;
+    scoef = RK(k1) * HI * de + RK(k10) * H2II * HI / 2.0 + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0 +
+            RK(k24s) * HI;
     if (rt) scoef = scoef + kphHI * HI;
-    acoef = r.k2 * de + r.k9 * HI + r.k11 * H2I / 2.0 + r.k16 * HM + r.k17 * HM;
+    acoef = RK(k2) * de + RK(k9) * HI + RK(k11) * H2I / 2.0 + RK(k16) * HM + RK(k17) * HM;
     HIIp = (scoef * dt + HII) / (1.0 + acoef * dt);
 
-    scoef = r.k8 * HM * HI + r.k15 * HM * HI + r.k17 * HM * HII + r.k57 * HI * HI +
-            r.k58 * HI * HeI / 4.0 + r.k24s * HIp + r.k25s * HeIIp / 4.0 + r.k26s * HeIp / 4.0;
+    scoef = RK(k8) * HM * HI + RK(k15) * HM * HI + RK(k17) * HM * HII + RK(k57) * HI * HI +
+            RK(k58) * HI * HeI / 4.0 + RK(k24s) * HIp + RK(k25s) * HeIIp / 4.0 + RK(k26s) * HeIp / 4.0;
     if (rt_all) scoef = scoef + kphHI * HIp + kphHeI * HeIp / 4.0 + kphHeII * HeIIp / 4.0;
     if (rt_honly) scoef = scoef + kphHI * HIp;
-    acoef = -(r.k1 * HI - r.k2 * HII + r.k3 * HeI / 4.0 - r.k6 * HeIII / 4.0 + r.k5 * HeII / 4.0 -
-              r.k4 * HeII / 4.0 + r.k14 * HM - r.k7 * HI - r.k18 * H2II / 2.0);
+    acoef = -(RK(k1) * HI - RK(k2) * HII + RK(k3) * HeI / 4.0 - RK(k6) * HeIII / 4.0 + RK(k5) * HeII / 4.0 -
+              RK(k4) * HeII / 4.0 + RK(k14) * HM - RK(k7) * HI - RK(k18) * H2II / 2.0);
     dep = (scoef * dt + de) / (1.0 + acoef * dt);
 
-    scoef = 2.0 * (r.k8 * HM * HI + r.k10 * H2II * HI / 2.0 + r.k19 * H2II * HM / 2.0 +
-                   r.k22 * HI * (HI * HI));
-    acoef = (r.k13 * HI + r.k11 * HII + r.k12 * de) + r.k29s + r.k31s;
-    if (anydust) scoef = scoef + 2.0 * r.h2dust * HI * th.rhoH;
+    scoef = 2.0 * (RK(k8) * HM * HI + RK(k10) * H2II * HI / 2.0 + RK(k19) * H2II * HM / 2.0 +
+                   RK(k22) * HI * (HI * HI));
+    acoef = (RK(k13) * HI + RK(k11) * HII + RK(k12) * de) + RK(k29s) + RK(k31s);
+    if (anydust) scoef = scoef + 2.0 * RK(h2dust) * HI * th.rhoH;
     H2Ip = (scoef * dt + H2I) / (1.0 + acoef * dt);
 
-    scoef = r.k7 * HI * de;
-    acoef = (r.k8 + r.k15) * HI + (r.k16 + r.k17) * HII + r.k14 * de + r.k19 * H2II / 2.0 + P.k27;
+    scoef = RK(k7) * HI * de;
+    acoef = (RK(k8) + RK(k15)) * HI + (RK(k16) + RK(k17)) * HII + RK(k14) * de + RK(k19) * H2II / 2.0 + P.k27;
     HMp = (scoef * dt + HM) / (1.0 + acoef * dt);
 
     // H2+ at equilibrium with the NEW abundances (:2293-2301)
-    H2IIp = 2.0 * (r.k9 * HIp * HIIp + r.k11 * H2Ip / 2.0 * HIIp + r.k17 * HMp * HIIp + r.k29s * H2Ip) /
-            (r.k10 * HIp + r.k18 * dep + r.k19 * HMp + (r.k28s + r.k30s));
+    H2IIp = 2.0 * (RK(k9) * HIp * HIIp + RK(k11) * H2Ip / 2.0 * HIIp + RK(k17) * HMp * HIIp + RK(k29s) * H2Ip) /
+            (RK(k10) * HIp + RK(k18) * dep + RK(k19) * HMp + (RK(k28s) + RK(k30s)));
   }
 
   if (PC > 2) {
     const double HM = c.HM, H2I = c.H2I, DI = c.DI, DII = c.DII, HDI = c.HDI;
-    scoef = (r.k2 * DII * de + r.k51 * DII * HI + 2.0 * r.k55 * HDI * HI / 3.0);
-    acoef = r.k1 * de + r.k50 * HII + r.k54 * H2I / 2.0 + r.k56 * HM + r.k24s;
+    scoef = (RK(k2) * DII * de + RK(k51) * DII * HI + 2.0 * RK(k55) * HDI * HI / 3.0);
+    acoef = RK(k1) * de + RK(k50) * HII + RK(k54) * H2I / 2.0 + RK(k56) * HM + RK(k24s);
     if (rt) acoef = acoef + kphHI;
     DIp = (scoef * dt + DI) / (1.0 + acoef * dt);
 
-    scoef = (r.k1 * DI * de + r.k50 * HII * DI + 2.0 * r.k53 * HII * HDI / 3.0) + r.k24s * DI;
+    scoef = (RK(k1) * DI * de + RK(k50) * HII * DI + 2.0 * RK(k53) * HII * HDI / 3.0) + RK(k24s) * DI;
     if (rt) scoef = scoef + kphHI * DI;
-    acoef = r.k2 * de + r.k51 * HI + r.k52 * H2I / 2.0;
+    acoef = RK(k2) * de + RK(k51) * HI + RK(k52) * H2I / 2.0;
     DIIp = (scoef * dt + DII) / (1.0 + acoef * dt);
 
-    scoef = 3.0 * (r.k52 * DII * H2I / 2.0 / 2.0 + r.k54 * DI * H2I / 2.0 / 2.0 +
-                   2.0 * r.k56 * DI * HM / 2.0);
-    acoef = r.k53 * HII + r.k55 * HI;
+    scoef = 3.0 * (RK(k52) * DII * H2I / 2.0 / 2.0 + RK(k54) * DI * H2I / 2.0 / 2.0 +
+                   2.0 * RK(k56) * DI * HM / 2.0);
+    acoef = RK(k53) * HII + RK(k55) * HI;
     HDIp = (scoef * dt + HDI) / (1.0 + acoef * dt);
   }
 

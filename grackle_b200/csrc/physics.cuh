@@ -19,6 +19,8 @@ namespace grb {
 #define GRB_TINY8 1.0e-40
 #define GRB_HUGE8 1.0e40
 #define GRB_MU_METAL 16.0
+// 1/ln(10) as the reference forms it: 1._DKIND / log(10._DKIND) (cool1d_cloudy_g.F:107)
+#define GRB_INV_LN10 (1.0 / 2.302585092994046)
 
 __device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
 __device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
@@ -26,6 +28,10 @@ __device__ __forceinline__ long long imin(long long a, long long b) { return a <
 __device__ __forceinline__ long long imax(long long a, long long b) { return a > b ? a : b; }
 __device__ __forceinline__ double ld(const double *p) { return __ldg(p); }
 __device__ __forceinline__ double sq(double x) { return x * x; }
+// x**y for x >= 0 as exp(y ln x): every real power on this path has a non-negative base.
+// |y ln x| < 1e2 here, so the result is within ~1e-14 relative of the correctly rounded
+// power (the tolerances are 1e-9 / 1e-6) at well under half the instructions of pow().
+__device__ __forceinline__ double pow_pos(double x, double y) { return exp(y * log(x)); }
 __device__ __forceinline__ double pow4(double x) { const double x2 = x * x; return x2 * x2; }
 
 // 1-based clamped index on a uniform axis (interpolators_g.F:28-29 and friends)
@@ -85,62 +91,29 @@ __device__ inline double interp3(const GrCloudyDev &c, const double *data, doubl
   return (in1 - ld(c.par[0] + i1 - 1)) * slope + v2[0];
 }
 
-// rank-3 (n_H, z, T) grid: linear in log(1+z) with the host-located z index
-__device__ inline double interp3z(const GrCloudyDev &c, const double *data, double in1, double zr,
-                                  double in3)
-{
-  const long long i1 = axis_index(in1, c.par[0], c.dpar[0], c.dim[0]);
-  const long long i3 = axis_index(in3, c.par[2], c.dpar[2], c.dim[2]);
-  const long long i2 = c.zindex;
-  const double x0 = ld(c.par[2] + i3 - 1), x1 = ld(c.par[2] + i3);
-  const double p0 = ld(c.par[0] + i1 - 1), p1 = ld(c.par[0] + i1);
-  if (c.end_int) {                       // interpolate_2Df3D_g
-    double v[2];
-#pragma unroll
-    for (int q = 1; q <= 2; q++)
-      v[q - 1] = lerp_last(data, ((q + i1 - 2) * c.dim[1] + (i2 - 1)) * c.dim[2] + i3, in3, x0, x1);
-    const double slope = (v[1] - v[0]) / (p1 - p0);
-    return (in1 - p0) * slope + v[0];
-  }
-  const double z0 = ld(c.par[1] + i2 - 1), z1 = ld(c.par[1] + i2);
-  const double zden = log((1 + z1) / (1 + z0));
-  const double znum = log((1 + zr) / (1 + z0));
-  double v2[2];
-#pragma unroll
-  for (int q = 1; q <= 2; q++) {
-    double v3[2];
-#pragma unroll
-    for (int w = 1; w <= 2; w++)
-      v3[w - 1] = lerp_last(data, ((q + i1 - 2) * c.dim[1] + (w + i2 - 2)) * c.dim[2] + i3, in3, x0, x1);
-    const double slope = (v3[1] - v3[0]) / zden;
-    v2[q - 1] = znum * slope + v3[0];
-  }
-  const double slope = (v2[1] - v2[0]) / (p1 - p0);
-  return (in1 - p0) * slope + v2[0];
-}
-
-// rank dispatch for new-style tables (cool1d_cloudy_g.F:157-236)
+// rank dispatch for new-style tables (cool1d_cloudy_g.F:157-236).  Rank-3 (n_H, z, T) grids
+// never reach the device: the host collapses them to the (n_H, T) plane at the call's
+// redshift (api.cu cloudy_params; interpolate_3Dz_g / interpolate_2Df3D_g semantics), so
+// a lookup is at most bilinear.
 __device__ inline double cloudy_lookup(const GrCloudyDev &c, const double *data, double log_n_h,
-                                       double zr, double log10T)
+                                       double log10T)
 {
   if (c.rank == 1) return interp1(c, data, log10T);
-  if (c.rank == 2) return interp2(c, data, log_n_h, log10T);
-  return interp3z(c, data, log_n_h, zr, log10T);
+  return interp2(c, data, log_n_h, log10T);
 }
 
 // ---- cool1d_cloudy_g (cool1d_cloudy_g.F:4-261): returns the edot increment -------
 __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, double rhoH,
                                      double metallicity, double logtem, int icmbTfloor, int iZscale)
 {
-  const double inv_log10 = 1.0 / log(10.0);
-  const double log10_tCMB = log10(P.comp2);
-  const double log10tem = logtem * inv_log10;
+  const double log10_tCMB = P.log10_tcmb;
+  const double log10tem = logtem * GRB_INV_LN10;
   const double log_n_h = log10(rhoH * P.dom);
-  double edot_met = -pow(10.0, cloudy_lookup(c, c.cooling, log_n_h, P.zr, log10tem));
+  double edot_met = -exp10(cloudy_lookup(c, c.cooling, log_n_h, log10tem));
   if (icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
-    edot_met = edot_met + pow(10.0, cloudy_lookup(c, c.cooling, log_n_h, P.zr, log10_tCMB));
+    edot_met = edot_met + exp10(cloudy_lookup(c, c.cooling, log_n_h, log10_tCMB));
   if (c.get_heat == 1)
-    edot_met = edot_met + pow(10.0, cloudy_lookup(c, c.heating, log_n_h, P.zr, log10tem));
+    edot_met = edot_met + exp10(cloudy_lookup(c, c.heating, log_n_h, log10tem));
   if (iZscale == 1) edot_met = edot_met * metallicity;
   return edot_met * rhoH * rhoH;
 }
@@ -150,9 +123,8 @@ __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, do
 __device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c, double d,
                                          double rhoH, double metallicity, double logtem)
 {
-  const double inv_log10 = 1.0 / log(10.0);
-  const double log10_tCMB = log10(P.comp2);      // see oracle note on the unassigned upstream local
-  const double log10tem = logtem * inv_log10;
+  const double log10_tCMB = P.log10_tcmb;        // see oracle note on the unassigned upstream local
+  const double log10tem = logtem * GRB_INV_LN10;
   double log_n_h = 0.0, log_Z = 0.0;
   if (c.rank > 1) log_n_h = log10(rhoH * P.dom);
   if (c.rank > 2) log_Z = log10(metallicity);
@@ -161,10 +133,10 @@ __device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c
     if (c.rank == 2) return interp2(c, data, log_n_h, lt);
     return interp3(c, data, log_n_h, log_Z, lt);
   };
-  double edot_met = -pow(10.0, look(c.cooling, log10tem));
+  double edot_met = -exp10(look(c.cooling, log10tem));
   if (P.icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
-    edot_met = edot_met + pow(10.0, look(c.cooling, log10_tCMB));
-  if (P.iClHeat == 1) edot_met = edot_met + pow(10.0, look(c.heating, log10tem));
+    edot_met = edot_met + exp10(look(c.cooling, log10_tCMB));
+  if (P.iClHeat == 1) edot_met = edot_met + exp10(look(c.heating, log10tem));
   return edot_met * rhoH * d;
 }
 
@@ -173,14 +145,14 @@ __device__ inline void temperature_table(const GrParams &P, double d, double e, 
                                          double rhoH, double &tgas, double &mmw)
 {
   const GrCloudyDev &c = P.pri;
-  const double inv_log10 = 1.0 / log(10.0);
+  const double inv_log10 = GRB_INV_LN10;
   const double log_n_h = log10(rhoH * P.dom);
   double munew = 1.0, muold = 1.0;
   for (int ti = 1; ti <= 20; ti++) {
     muold = munew;
     tgas = dmax((P.gamma - 1.0) * e * munew * P.utem, P.temstart);
     const double log10tem = log(tgas) * inv_log10;
-    munew = cloudy_lookup(c, c.mmw, log_n_h, P.zr, log10tem);
+    munew = cloudy_lookup(c, c.mmw, log_n_h, log10tem);
     munew = 0.5 * (munew + muold);
     tgas = tgas * munew / muold;
     if (fabs((munew / muold) - 1.0) <= 1.e-2) {
@@ -224,7 +196,7 @@ __device__ inline double dust_temperature(double tgas, double nh, double gasgr, 
   } else if (tgas > t_subl) {
     newton = false;
   } else {
-    td = dmax(trad, pow(gamma_isrf / radf / kgr1, 0.17));
+    td = dmax(trad, pow_pos(gamma_isrf / radf / kgr1, 0.17));
   }
   for (int it = 1; it <= 50 && newton; it++) {
     const double tdp = dmax(1.e-3, ((1.0 + pert) * td));

@@ -1388,9 +1388,11 @@ void make_consistent_g(const FArgs &a)
 long long g_subcycles_sum = 0, g_subcycles_max = 0;
 
 // Conditioning probe (test harness only, OFF by default => bit-exact reference algorithm):
-// multiply edot by (1 + amp*u), u in [-1,1] hashed from (cell, iter, seed), in every
-// subcycle.  Running the oracle against itself with amp ~ 1e-15 tells which cells' answers
-// are reproducible under round-off-level changes and which are chaotic (limit cycles).
+// multiply edot by (1 + amp*u) and tgas by (1 + 0.01*amp*u'), u in [-1,1] hashed from
+// (cell, iter, seed), in every subcycle.  Running the oracle against itself with
+// amp ~ 1e-13 (edot is a difference of nearly cancelling sums near thermal balance, so a
+// 1-ulp change of one term is a 1e-14..1e-12 relative change of edot) tells which cells'
+// answers are reproducible under round-off-level changes and which are chaotic.
 double g_noise_amp = 0.0;
 unsigned long long g_noise_seed = 0;
 inline double noise_unit(unsigned long long a, unsigned long long b, unsigned long long c)
@@ -1454,7 +1456,11 @@ void solve_rate_cool(const FArgs &a, int *ierr)
       cool1d_multi_g(a, r, j, k, iter, comp1, comp2);
       if (g_noise_amp != 0.0)
         for (int i = is; i <= ie; i++) if (r.itmask[i])
+        {
           r.edot[i] *= 1.0 + g_noise_amp * noise_unit(IDX(a, i, j, k), (unsigned long long)iter, g_noise_seed);
+          // and 1 % of that on the temperature the rate lookup sees (models libm log/exp ulps)
+          r.tgas[i] *= 1.0 + 0.01 * g_noise_amp * noise_unit(IDX(a, i, j, k), (unsigned long long)iter, g_noise_seed + 77);
+        }
 
       if (a.ispecies > 0) {
         lookup_cool_rates1d_g(a, r, j, k, anydust, dom, coolunit, tbase1, xbase1, dx_cgs, c_ljeans);
