@@ -28,6 +28,26 @@ __device__ __forceinline__ double lerp_row(const double *row, int ncol, int col,
   return a + (b - a) * t;
 }
 
+// N (even) consecutive columns starting at the even column C0: all 2*N/2 double2 loads are
+// issued before the first lerp, so a cell pays ONE table round trip per column group
+// instead of one per column (ncu round 1: 77 % of the long-scoreboard stall cycles sat on
+// the dependent DADD of the one-at-a-time lerp).
+template <int NCOL, int C0, int N>
+__device__ __forceinline__ void lerp_cols(const double *row, double t, double (&out)[N])
+{
+  static_assert((C0 % 2) == 0 && (N % 2) == 0 && (NCOL % 2) == 0, "double2 alignment");
+  double2 a[N / 2], b[N / 2];
+  const double2 *p0 = reinterpret_cast<const double2 *>(row + C0);
+  const double2 *p1 = reinterpret_cast<const double2 *>(row + NCOL + C0);
+#pragma unroll
+  for (int i = 0; i < N / 2; i++) { a[i] = __ldg(p0 + i); b[i] = __ldg(p1 + i); }
+#pragma unroll
+  for (int i = 0; i < N / 2; i++) {
+    out[2 * i] = a[i].x + (b[i].x - a[i].x) * t;
+    out[2 * i + 1] = a[i].y + (b[i].y - a[i].y) * t;
+  }
+}
+
 // Rahmati+13 eq. 13/14 shielding fraction (cool1d_multi_g.F:788-792, solve_rate_cool_g.F:1518-1520)
 __device__ __forceinline__ double rahmati_f(double nratio)
 {
@@ -114,11 +134,13 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
 #define COOL_LERP(col) lerp_row(row, NCOOL, col, tdef)
 
   if (PC > 0) {     // six-species atomic cooling (:417-446)
-    const double ceHI = COOL_LERP(L_CEHI), ceHeI = COOL_LERP(L_CEHEI), ceHeII = COOL_LERP(L_CEHEII);
-    const double ciHI = COOL_LERP(L_CIHI), ciHeI = COOL_LERP(L_CIHEI), ciHeIS = COOL_LERP(L_CIHEIS);
-    const double ciHeII = COOL_LERP(L_CIHEII), reHII = COOL_LERP(L_REHII);
-    const double reHeII1 = COOL_LERP(L_REHEII1), reHeII2 = COOL_LERP(L_REHEII2);
-    const double reHeIII = COOL_LERP(L_REHEIII), brem = COOL_LERP(L_BREM);
+    double at[12];
+    lerp_cols<NCOOL, L_CEHI, 12>(row, tdef, at);
+    const double ceHI = at[L_CEHI], ceHeI = at[L_CEHEI], ceHeII = at[L_CEHEII];
+    const double ciHI = at[L_CIHI], ciHeI = at[L_CIHEI], ciHeIS = at[L_CIHEIS];
+    const double ciHeII = at[L_CIHEII], reHII = at[L_REHII];
+    const double reHeII1 = at[L_REHEII1], reHeII2 = at[L_REHEII2];
+    const double reHeIII = at[L_REHEIII], brem = at[L_BREM];
     const double de = c.de;
     edot = (- ceHI * c.HI * de
             - ceHeI * c.HeII * (de * de) * dom / 4.0
@@ -135,8 +157,9 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   }
 
   if (PC > 1) {     // H2 cooling, Glover & Abel (2008) (:472-526), CIE (:630-649)
-    const double gaHI = COOL_LERP(L_GAHI), gaH2 = COOL_LERP(L_GAH2), gaHe = COOL_LERP(L_GAHE);
-    const double gaHp = COOL_LERP(L_GAHP), gael = COOL_LERP(L_GAEL), h2lte = COOL_LERP(L_H2LTE);
+    double ga[6];
+    lerp_cols<NCOOL, L_GAHI, 6>(row, tdef, ga);
+    const double gaHI = ga[0], gaH2 = ga[1], gaHe = ga[2], gaHp = ga[3], gael = ga[4], h2lte = ga[5];
     double fudge = 1.0;
     if (P.ih2optical == 1) {
       fudge = pow_pos(0.76 * c.d * dom / 8.e9, -0.45);
@@ -159,7 +182,7 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
 
   if (PC > 2) {     // HD cooling (:655-686)
     double hdlte, hdlow;
-    if (th.tgas > P.comp2) { hdlte = COOL_LERP(L_HDLTE); hdlow = COOL_LERP(L_HDLOW); }
+    if (th.tgas > P.comp2) { double hd[2]; lerp_cols<NCOOL, L_HDLTE, 2>(row, tdef, hd); hdlte = hd[0]; hdlow = hd[1]; }
     else { hdlte = GRB_TINY; hdlow = GRB_TINY; }
     const double hdlte1 = hdlte / (c.HI * dom);
     const double hdlow1 = dmax(hdlow, GRB_TINY);

@@ -6,10 +6,10 @@
 //    one active cell; a warp reads 32 consecutive i => 256-byte coalesced segments.
 //  * Per-T tables: re-packed from the reference's 70 separate 600-entry arrays
 //    (chemistry_data_storage) into two row-major matrices
-//        chem[bin][NCHEM]   (k1..k58, ncr*, k13dd*14)      600 x 46 doubles = 221 KB
+//        chem[bin][NCHEM]   (k1..k58, ncr*, k13dd*14)      600 x 48 doubles = 230 KB
 //        cool[bin][NCOOL]   (ceHI..brem, GA*, H2LTE, ...)  600 x 24 doubles = 115 KB
 //    so the two bins a cell interpolates between are ONE contiguous span
-//    (2 x 368 B resp. 2 x 192 B) instead of 92 scattered 8-byte gathers.
+//    (2 x 384 B resp. 2 x 192 B, fetched as double2) instead of 92 scattered 8-byte gathers.
 //  * h2dust[dustbin][bin] (1.2 MB) and the Cloudy grids stay in the reference's
 //    order (T fastest) and are read through the read-only path (L2-resident).
 #ifndef GRB200_DEVICE_H
@@ -17,23 +17,27 @@
 
 #include <cstdint>
 
-// column indices of the packed chemistry-rate matrix
+// column indices of the packed chemistry-rate matrix.  A row is 48 doubles = 384 B = three
+// 128-byte lines; column groups start on even columns so they can be fetched as double2.
 enum {
   C_K1 = 0, C_K2, C_K3, C_K4, C_K5, C_K6, C_K57, C_K58,          // 6-species network
   C_K7, C_K8, C_K9, C_K10, C_K11, C_K12, C_K13, C_K14, C_K15,    // + H2
   C_K16, C_K17, C_K18, C_K19, C_K22, C_NCRN, C_NCRD1, C_NCRD2,
+  C_PAD0,
   C_K13DD0,                                                       // 14 columns
   C_K50 = C_K13DD0 + 14, C_K51, C_K52, C_K53, C_K54, C_K55, C_K56,  // + D
+  C_PAD1,
   NCHEM
 };
-static_assert(NCHEM == 46, "packed chemistry row is 46 doubles");
+static_assert(NCHEM == 48 && C_K13DD0 == 26 && C_K50 == 40, "packed chemistry row is 48 doubles");
 
-// column indices of the packed cooling-rate matrix
+// column indices of the packed cooling-rate matrix (24 doubles = 192 B per row)
 enum {
   L_CEHI = 0, L_CEHEI, L_CEHEII, L_CIHI, L_CIHEI, L_CIHEIS, L_CIHEII,
-  L_REHII, L_REHEII1, L_REHEII2, L_REHEIII, L_BREM,
-  L_GAHI, L_GAH2, L_GAHE, L_GAHP, L_GAEL, L_H2LTE, L_CIECO,
-  L_HDLTE, L_HDLOW, L_GASGR, L_REGR, L_PAD,
+  L_REHII, L_REHEII1, L_REHEII2, L_REHEIII, L_BREM,              // [0,12)  atomic
+  L_GAHI, L_GAH2, L_GAHE, L_GAHP, L_GAEL, L_H2LTE,               // [12,18) H2
+  L_HDLTE, L_HDLOW,                                              // [18,20) HD
+  L_CIECO, L_GASGR, L_REGR, L_PAD,
   NCOOL
 };
 static_assert(NCOOL == 24, "packed cooling row is 24 doubles");

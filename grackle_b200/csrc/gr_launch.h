@@ -5,7 +5,7 @@
 #include "gr_device.h"
 
 #ifndef GRB_SOLVE_THREADS
-#define GRB_SOLVE_THREADS 128
+#define GRB_SOLVE_THREADS 512    /* one CTA per SM: 16 warps, <=128 registers per thread */
 #endif
 #ifndef GRB_SOLVE_MINBLOCKS
 #define GRB_SOLVE_MINBLOCKS 1     /* resident CTAs per SM the register allocator must allow */

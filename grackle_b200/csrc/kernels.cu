@@ -348,14 +348,30 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 // L2 on their own (ncu round 1: 55 % of all stall cycles were stall_no_inst).  Barriers
 // between the stages keep the warps of a CTA inside the same few KB of code, so one warp's
 // fetch serves all of them.
-#ifndef GRB_LOCKSTEP
-#define GRB_LOCKSTEP 1
+// The CTA is split into lockstep groups of GRB_GROUP_WARPS warps, each on its own named
+// barrier: inside a group one warp's instruction fetch serves all, while the groups run out
+// of phase with each other so one group's barrier tail is covered by the others' work.
+#ifndef GRB_GROUP_WARPS
+#define GRB_GROUP_WARPS 8
 #endif
-#if GRB_LOCKSTEP
-#define GRB_ALIGN() __syncthreads()
-#else
-#define GRB_ALIGN() ((void)0)
-#endif
+static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0, "CTA must be whole lockstep groups");
+static_assert(GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15, "named barriers 1..15");
+
+__device__ __forceinline__ void group_align(int bar_id)
+{
+  asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(32 * GRB_GROUP_WARPS) : "memory");
+}
+// barrier + OR-reduction of a predicate over the group
+__device__ __forceinline__ bool group_any(int bar_id, bool pred)
+{
+  int out;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.s32 q, %3, 0;\n\tbar.red.or.pred p, %1, %2, q;\n\tselp.s32 %0, 1, 0, p;\n\t}"
+      : "=r"(out)
+      : "r"(bar_id), "r"(32 * GRB_GROUP_WARPS), "r"((int)pred)
+      : "memory");
+  return out != 0;
+}
 
 template <int PC>
 __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P)
@@ -364,6 +380,7 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
   const Rates r{rate_slots + threadIdx.x};
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
+  const int bar_id = 1 + (int)(threadIdx.x >> 5) / GRB_GROUP_WARPS;
   Cell c;
   SubState s;
   size_t x = 0;
@@ -398,24 +415,17 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
       }
     }
     // after the refill every lane either owns a cell or has seen the end of the queue
-#if GRB_LOCKSTEP
-    if (__syncthreads_or(active ? 1 : 0) == 0) break;
-#else
-    if (__ballot_sync(full, active) == 0) {
-      if (__ballot_sync(full, !exhausted) == 0) break;
-      continue;
-    }
-#endif
+    if (!group_any(bar_id, active)) break;
     // ---- one subcycle on every busy lane ----
     Thermo th;
     if (active) {
       load_extras<PC>(P, x, c);
       cool_rate<PC>(P, c, s.iter == 1, s.tgasold, th);
     }
-    GRB_ALIGN();
+    group_align(bar_id);
     if (PC > 0) {
       if (active) subcycle_lookup<PC>(P, c, th, x, r);
-      GRB_ALIGN();
+      group_align(bar_id);
     }
     if (active) {
       const bool done = subcycle_finish<PC>(P, c, s, th, r);

@@ -61,6 +61,9 @@ struct Rates {
   double *base;    // shared memory, already offset by threadIdx.x
 };
 #define RK(name) (r.base[RI_##name * GRB_SOLVE_THREADS])
+static_assert(RI_k58 - RI_k1 == C_K58 - C_K1 && RI_k16 - RI_k7 == C_K16 - C_K7 &&
+              RI_ncrd2 - RI_k17 == C_NCRD2 - C_K17 && RI_k56 - RI_k50 == C_K56 - C_K50,
+              "rate slots must follow the packed column order");
 
 // neighbour densities for the Sobolev-like H2 shielding length (H2_self_shielding == 1)
 struct Neigh { double d[6]; };
@@ -83,19 +86,29 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
   const double *row = P.chem + (size_t)(ti.idx - 1) * NCHEM;
 #define K_LERP(col) lerp_row(row, NCHEM, col, tdef)
 
-  RK(k1) = K_LERP(C_K1); RK(k2) = K_LERP(C_K2); RK(k3) = K_LERP(C_K3); RK(k4) = K_LERP(C_K4);
-  RK(k5) = K_LERP(C_K5); RK(k6) = K_LERP(C_K6); RK(k57) = K_LERP(C_K57); RK(k58) = K_LERP(C_K58);
-
+  // slots RI_k1.. follow the column order of the packed row, so a column group lands in
+  // consecutive slots
+  {
+    double v[8];
+    lerp_cols<NCHEM, C_K1, 8>(row, tdef, v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.base[(RI_k1 + i) * GRB_SOLVE_THREADS] = v[i];
+  }
   if (PC > 1) {
-    RK(k7) = K_LERP(C_K7); RK(k8) = K_LERP(C_K8); RK(k9) = K_LERP(C_K9); RK(k10) = K_LERP(C_K10);
-    RK(k11) = K_LERP(C_K11); RK(k12) = K_LERP(C_K12); RK(k13) = K_LERP(C_K13); RK(k14) = K_LERP(C_K14);
-    RK(k15) = K_LERP(C_K15); RK(k16) = K_LERP(C_K16); RK(k17) = K_LERP(C_K17); RK(k18) = K_LERP(C_K18);
-    RK(k19) = K_LERP(C_K19); RK(k22) = K_LERP(C_K22);
-    RK(ncrn) = K_LERP(C_NCRN); RK(ncrd1) = K_LERP(C_NCRD1); RK(ncrd2) = K_LERP(C_NCRD2);
+    double v[10];
+    lerp_cols<NCHEM, C_K7, 10>(row, tdef, v);                 // k7 .. k16
+#pragma unroll
+    for (int i = 0; i < 10; i++) r.base[(RI_k7 + i) * GRB_SOLVE_THREADS] = v[i];
+    double w[8];
+    lerp_cols<NCHEM, C_K17, 8>(row, tdef, w);                 // k17 k18 k19 k22 ncr_n ncr_d1 ncr_d2 (pad)
+#pragma unroll
+    for (int i = 0; i < 7; i++) r.base[(RI_k17 + i) * GRB_SOLVE_THREADS] = w[i];
   }
   if (PC > 2) {
-    RK(k50) = K_LERP(C_K50); RK(k51) = K_LERP(C_K51); RK(k52) = K_LERP(C_K52); RK(k53) = K_LERP(C_K53);
-    RK(k54) = K_LERP(C_K54); RK(k55) = K_LERP(C_K55); RK(k56) = K_LERP(C_K56);
+    double v[8];
+    lerp_cols<NCHEM, C_K50, 8>(row, tdef, v);                 // k50 .. k56 (pad)
+#pragma unroll
+    for (int i = 0; i < 7; i++) r.base[(RI_k50 + i) * GRB_SOLVE_THREADS] = v[i];
   }
 
   // H2 formation on grains: bilinear in (ln T, ln T_dust) (:1327-1378)
@@ -188,8 +201,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
     RK(k13) = GRB_TINY8;
     if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
       double dd[14];
-#pragma unroll
-      for (int n = 0; n < 14; n++) dd[n] = K_LERP(C_K13DD0 + n);
+      lerp_cols<NCHEM, C_K13DD0, 14>(row, tdef, dd);
       double cid = dd[0] - dd[1] / (1.0 + pow_pos(nh / dd[4], dd[6])) + dd[2] -
                    dd[3] / (1.0 + pow_pos(nh / dd[5], dd[6]));
       cid = dmax(exp10(cid), GRB_TINY8);
