@@ -17,6 +17,7 @@ struct Cell {
 // what cool_rate leaves behind for the rest of the subcycle (the reference's row temporaries)
 struct Thermo {
   double edot, tgas, mmw, p2d, tdust, metallicity, dust2gas, rhoH, myde;
+  double logtgas;     // ln(tgas), formed once here and reused by the rate lookup
 };
 
 // two adjacent rows of a packed table -> lerp of column `col`
@@ -72,7 +73,7 @@ __device__ __forceinline__ TIndex t_index(const GrParams &P, double logtem)
 // ---------------------------------------------------------------------------------
 template <int PC>
 __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, double &tgasold,
-                                 Thermo &th)
+                                 Thermo &th, bool lookup_follows = true)
 {
   const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
   const double dom = P.dom, dom_inv = P.dom_inv;
@@ -118,6 +119,9 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   if (P.imetal == 1) th.metallicity = c.metal / c.d / P.z_solar;
   const double mynh = th.rhoH * dom;
   if (first) tgasold = th.tgas;
+
+  // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211)
+  th.logtgas = (PC > 0 && lookup_follows) ? log(th.tgas) : 0.0;
 
   double logtem = log(0.5 * (th.tgas + tgasold));
   logtem = dmax(logtem, P.logtem0);

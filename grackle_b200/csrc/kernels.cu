@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ Gr
   load_cell<PC>(P, x, c, false);
   Thermo th;
   double tgasold = 0.0;
-  cool_rate<PC>(P, c, true, tgasold, th);
+  cool_rate<PC>(P, c, true, tgasold, th, false);
   const double energy = dmax(th.p2d / (P.gamma - 1.0), GRB_TINY);
   P.out[x] = energy / th.edot;
 }
@@ -273,12 +273,12 @@ __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubS
       const int ridx = (int)RK(idx);
       const double k22lo = ld(P.k22a + ridx - 1), k22hi = ld(P.k22a + ridx);
       const double k13lo = ld(P.k13a + ridx - 1), k13hi = ld(P.k13a + ridx);
-      const double eqt2 = dmin(log(th.tgas) + 0.1 * P.dlogtem, RK(t2));
+      const double eqt2 = dmin(th.logtgas + 0.1 * P.dlogtem, RK(t2));
       double eqtdef = (eqt2 - RK(t1)) / (RK(t2) - RK(t1));
       const double eqk222 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk132 = k13lo + (k13hi - k13lo) * eqtdef;
       const double heq2 = (-1.0 / (4.0 * eqk222)) * (eqk132 - sqrt(8.0 * eqk132 * eqk222 * fd + eqk132 * eqk132));
-      const double eqt1 = dmax(log(th.tgas) - 0.1 * P.dlogtem, RK(t1));
+      const double eqt1 = dmax(th.logtgas - 0.1 * P.dlogtem, RK(t1));
       eqtdef = (eqt1 - RK(t1)) / (RK(t2) - RK(t1));
       const double eqk221 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk131 = k13lo + (k13hi - k13lo) * eqtdef;
@@ -351,6 +351,9 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 // The CTA is split into lockstep groups of GRB_GROUP_WARPS warps, each on its own named
 // barrier: inside a group one warp's instruction fetch serves all, while the groups run out
 // of phase with each other so one group's barrier tail is covered by the others' work.
+#ifndef GRB_STAGE_BARRIERS
+#define GRB_STAGE_BARRIERS 0      /* extra re-alignment points inside a subcycle (measured: 0 is fastest) */
+#endif
 #ifndef GRB_GROUP_WARPS
 #define GRB_GROUP_WARPS 8
 #endif
@@ -422,10 +425,14 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
       load_extras<PC>(P, x, c);
       cool_rate<PC>(P, c, s.iter == 1, s.tgasold, th);
     }
+#if GRB_STAGE_BARRIERS >= 2
     group_align(bar_id);
+#endif
     if (PC > 0) {
       if (active) subcycle_lookup<PC>(P, c, th, x, r);
+#if GRB_STAGE_BARRIERS >= 1
       group_align(bar_id);
+#endif
     }
     if (active) {
       const bool done = subcycle_finish<PC>(P, c, s, th, r);

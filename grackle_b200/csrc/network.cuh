@@ -77,7 +77,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
 {
   const bool anydust = (P.idust > 0) || (P.idustall > 0);
   const double dom = P.dom;
-  double logtem = log(th.tgas);
+  double logtem = th.logtgas;          // = log(th.tgas), formed in cool_rate
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
   const TIndex ti = t_index(P, logtem);
