@@ -123,16 +123,16 @@ int upload_tables(DeviceCtx *ctx, const chemistry_data *chem, const chemistry_da
   if (chem->primordial_chemistry > 0) {
     std::vector<double> m((size_t)nb * NCHEM, 0.0);
     const double *cols[NCHEM] = {nullptr};
-    cols[C_K1] = r->k1; cols[C_K2] = r->k2; cols[C_K3] = r->k3; cols[C_K4] = r->k4;
-    cols[C_K5] = r->k5; cols[C_K6] = r->k6; cols[C_K57] = r->k57; cols[C_K58] = r->k58;
-    cols[C_K7] = r->k7; cols[C_K8] = r->k8; cols[C_K9] = r->k9; cols[C_K10] = r->k10;
-    cols[C_K11] = r->k11; cols[C_K12] = r->k12; cols[C_K13] = r->k13; cols[C_K14] = r->k14;
-    cols[C_K15] = r->k15; cols[C_K16] = r->k16; cols[C_K17] = r->k17; cols[C_K18] = r->k18;
-    cols[C_K19] = r->k19; cols[C_K22] = r->k22; cols[C_NCRN] = r->n_cr_n;
-    cols[C_NCRD1] = r->n_cr_d1; cols[C_NCRD2] = r->n_cr_d2;
+    cols[C_k1] = r->k1; cols[C_k2] = r->k2; cols[C_k3] = r->k3; cols[C_k4] = r->k4;
+    cols[C_k5] = r->k5; cols[C_k6] = r->k6; cols[C_k57] = r->k57; cols[C_k58] = r->k58;
+    cols[C_k7] = r->k7; cols[C_k8] = r->k8; cols[C_k9] = r->k9; cols[C_k10] = r->k10;
+    cols[C_k11] = r->k11; cols[C_k12] = r->k12; cols[C_k13] = r->k13; cols[C_k14] = r->k14;
+    cols[C_k15] = r->k15; cols[C_k16] = r->k16; cols[C_k17] = r->k17; cols[C_k18] = r->k18;
+    cols[C_k19] = r->k19; cols[C_k22] = r->k22; cols[C_ncrn] = r->n_cr_n;
+    cols[C_ncrd1] = r->n_cr_d1; cols[C_ncrd2] = r->n_cr_d2;
     for (int n = 0; n < 14; n++) cols[C_K13DD0 + n] = r->k13dd + (size_t)n * nb;
-    cols[C_K50] = r->k50; cols[C_K51] = r->k51; cols[C_K52] = r->k52; cols[C_K53] = r->k53;
-    cols[C_K54] = r->k54; cols[C_K55] = r->k55; cols[C_K56] = r->k56;
+    cols[C_k50] = r->k50; cols[C_k51] = r->k51; cols[C_k52] = r->k52; cols[C_k53] = r->k53;
+    cols[C_k54] = r->k54; cols[C_k55] = r->k55; cols[C_k56] = r->k56;
     for (int c = 0; c < NCHEM; c++)
       if (cols[c])
         for (int b = 0; b < nb; b++) m[(size_t)b * NCHEM + c] = cols[c][b];

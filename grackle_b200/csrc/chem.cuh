@@ -68,16 +68,19 @@ __device__ __forceinline__ TIndex t_index(const GrParams &P, double logtem)
 }
 
 // ---------------------------------------------------------------------------------
-// cool1d_multi_g (cool1d_multi_g.F:6-1131) for one cell.  `first` = (iter == 1).
-// tgasold is the per-cell carry between subcycles.
+// cool1d_multi_g (cool1d_multi_g.F:6-1131) for one cell, in two parts so that the solve
+// kernel can fetch the cooling-table rows between them:
+//   thermo_head : temperature, mean molecular weight, ... (:212-357); returns the clamped
+//                 ln of the temperature the cooling tables are read at
+//   cool_sums   : every cooling / heating term (:360-1131).  CV supplies the interpolated
+//                 value of cooling-table column `col` (registers for the one-shot
+//                 calculate_* kernels, shared-memory slots in the solve kernel).
+// `first` = (iter == 1).  tgasold is the per-cell carry between subcycles.
 // ---------------------------------------------------------------------------------
 template <int PC>
-__device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, double &tgasold,
-                                 Thermo &th, bool lookup_follows = true)
+__device__ inline double thermo_head(const GrParams &P, const Cell &c, bool first, double &tgasold,
+                                     Thermo &th, bool lookup_follows)
 {
-  const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
-  const double dom = P.dom, dom_inv = P.dom_inv;
-  double edot = 0.0;
   th.p2d = (P.gamma - 1.0) * c.d * c.e;
   th.tdust = 0.0; th.metallicity = 0.0; th.dust2gas = 0.0;
 
@@ -117,7 +120,6 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   }
 
   if (P.imetal == 1) th.metallicity = c.metal / c.d / P.z_solar;
-  const double mynh = th.rhoH * dom;
   if (first) tgasold = th.tgas;
 
   // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211)
@@ -126,25 +128,30 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   double logtem = log(0.5 * (th.tgas + tgasold));
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
+  return logtem;
+}
 
-  const bool interp = (PC > 0) || (P.idustall > 0);
-  const double *row = P.cool;
-  double tdef = 0.0;
-  if (interp) {
-    const TIndex ti = t_index(P, logtem);
-    row = P.cool + (size_t)(ti.idx - 1) * NCOOL;
-    tdef = ti.tdef;
-  }
-#define COOL_LERP(col) lerp_row(row, NCOOL, col, tdef)
+// cooling-table values of one cell held in registers (one-shot kernels)
+struct CoolRegs {
+  double v[NCOOL];
+  __device__ __forceinline__ double operator()(int col) const { return v[col]; }
+};
+
+template <int PC, class CV>
+__device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem, const CV &cv,
+                                 double &tgasold, Thermo &th)
+{
+  const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
+  const double dom = P.dom, dom_inv = P.dom_inv;
+  double edot = 0.0;
+  const double mynh = th.rhoH * dom;
 
   if (PC > 0) {     // six-species atomic cooling (:417-446)
-    double at[12];
-    lerp_cols<NCOOL, L_CEHI, 12>(row, tdef, at);
-    const double ceHI = at[L_CEHI], ceHeI = at[L_CEHEI], ceHeII = at[L_CEHEII];
-    const double ciHI = at[L_CIHI], ciHeI = at[L_CIHEI], ciHeIS = at[L_CIHEIS];
-    const double ciHeII = at[L_CIHEII], reHII = at[L_REHII];
-    const double reHeII1 = at[L_REHEII1], reHeII2 = at[L_REHEII2];
-    const double reHeIII = at[L_REHEIII], brem = at[L_BREM];
+    const double ceHI = cv(L_CEHI), ceHeI = cv(L_CEHEI), ceHeII = cv(L_CEHEII);
+    const double ciHI = cv(L_CIHI), ciHeI = cv(L_CIHEI), ciHeIS = cv(L_CIHEIS);
+    const double ciHeII = cv(L_CIHEII), reHII = cv(L_REHII);
+    const double reHeII1 = cv(L_REHEII1), reHeII2 = cv(L_REHEII2);
+    const double reHeIII = cv(L_REHEIII), brem = cv(L_BREM);
     const double de = c.de;
     edot = (- ceHI * c.HI * de
             - ceHeI * c.HeII * (de * de) * dom / 4.0
@@ -161,9 +168,8 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   }
 
   if (PC > 1) {     // H2 cooling, Glover & Abel (2008) (:472-526), CIE (:630-649)
-    double ga[6];
-    lerp_cols<NCOOL, L_GAHI, 6>(row, tdef, ga);
-    const double gaHI = ga[0], gaH2 = ga[1], gaHe = ga[2], gaHp = ga[3], gael = ga[4], h2lte = ga[5];
+    const double gaHI = cv(L_GAHI), gaH2 = cv(L_GAH2), gaHe = cv(L_GAHE), gaHp = cv(L_GAHP);
+    const double gael = cv(L_GAEL), h2lte = cv(L_H2LTE);
     double fudge = 1.0;
     if (P.ih2optical == 1) {
       fudge = pow_pos(0.76 * c.d * dom / 8.e9, -0.45);
@@ -173,7 +179,7 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
     const double gphdl1 = h2lte / dom;
     edot = edot - (double)P.ih2co * fudge * c.H2I * h2lte / (1.0 + gphdl1 / galdl) / (2.0 * dom);
     if (P.iciecool == 1 && c.d * dom > 1e10) {
-      const double cieco = COOL_LERP(L_CIECO);
+      const double cieco = cv(L_CIECO);
       double tau = pow_pos((c.d / 2e16) * dom, 2.8);
       tau = dmax(tau, 1.e-5);
       double ciefudge = dmin((1.0 - exp(-tau)) / tau, 1.0);
@@ -186,7 +192,7 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
 
   if (PC > 2) {     // HD cooling (:655-686)
     double hdlte, hdlow;
-    if (th.tgas > P.comp2) { double hd[2]; lerp_cols<NCOOL, L_HDLTE, 2>(row, tdef, hd); hdlte = hd[0]; hdlow = hd[1]; }
+    if (th.tgas > P.comp2) { hdlte = cv(L_HDLTE); hdlow = cv(L_HDLOW); }
     else { hdlte = GRB_TINY; hdlow = GRB_TINY; }
     const double hdlte1 = hdlte / (c.HI * dom);
     const double hdlow1 = dmax(hdlow, GRB_TINY);
@@ -199,7 +205,7 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   if (anydust || (P.igammah > 1)) myisrf = (P.iisrffield > 0) ? c.isrf : P.isrf;
 
   if (anydust) {    // gas-grain heat transfer and T_dust (:726-753)
-    const double gasgr = COOL_LERP(L_GASGR);
+    const double gasgr = cv(L_GASGR);
     const double gasgr_tdust = P.fgr * gasgr * P.coolunit / GRB_MASS_H;
     th.tdust = dust_temperature(th.tgas, mynh, gasgr_tdust, P.gamma_isrfa, myisrf, P.comp2);
     edot = edot - gasgr * (th.tgas - th.tdust) * th.dust2gas * th.rhoH * th.rhoH;
@@ -250,7 +256,7 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   }
 
   if ((P.idustall > 0) || (P.idustrec > 0)) {   // grain recombination cooling (:1005-1023)
-    const double regr = COOL_LERP(L_REGR);
+    const double regr = cv(L_REGR);
     const double grbeta = 0.74 / pow_pos(th.tgas, 0.068);
     edot = edot - regr * pow_pos(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
   }
@@ -269,10 +275,54 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
 
   if (P.iVheat == 1) edot = edot + c.vheat / P.coolunit / (dom * dom);
   if (P.iMheat == 1) edot = edot + c.mheat * c.d * GRB_MASS_H / P.coolunit / dom;
-#undef COOL_LERP
 
   tgasold = th.tgas;
   th.edot = edot;
+}
+
+// the whole of cool1d_multi_g for a kernel that evaluates it once per cell: the table
+// values come straight from global memory, all loads of a column group in flight together
+template <int PC>
+__device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, double &tgasold,
+                                 Thermo &th, bool lookup_follows = true)
+{
+  const double logtem = thermo_head<PC>(P, c, first, tgasold, th, lookup_follows);
+  const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
+  CoolRegs cv;
+#pragma unroll
+  for (int i = 0; i < NCOOL; i++) cv.v[i] = 0.0;
+  // the table index is only formed when species or the full dust model are on (:349-357);
+  // otherwise the first bin is read as it stands
+  const double *row = P.cool;
+  double tdef = 0.0;
+  if ((PC > 0) || (P.idustall > 0)) {
+    const TIndex ti = t_index(P, logtem);
+    row = P.cool + (size_t)(ti.idx - 1) * NCOOL;
+    tdef = ti.tdef;
+  }
+  if (PC > 0) {
+    double at[12];
+    lerp_cols<NCOOL, L_CEHI, 12>(row, tdef, at);
+#pragma unroll
+    for (int i = 0; i < 12; i++) cv.v[L_CEHI + i] = at[i];
+  }
+  if (PC > 1) {
+    double ga[6];
+    lerp_cols<NCOOL, L_GAHI, 6>(row, tdef, ga);
+#pragma unroll
+    for (int i = 0; i < 6; i++) cv.v[L_GAHI + i] = ga[i];
+    if (P.iciecool == 1) cv.v[L_CIECO] = lerp_row(row, NCOOL, L_CIECO, tdef);
+  }
+  if (PC > 2) {
+    double hd[2];
+    lerp_cols<NCOOL, L_HDLTE, 2>(row, tdef, hd);
+    cv.v[L_HDLTE] = hd[0]; cv.v[L_HDLOW] = hd[1];
+  }
+  if (anydust) {
+    cv.v[L_GASGR] = lerp_row(row, NCOOL, L_GASGR, tdef);
+    cv.v[L_REGR] = lerp_row(row, NCOOL, L_REGR, tdef);
+  }
+  cool_sums<PC>(P, c, logtem, cv, tgasold, th);
 }
 
 }  // namespace grb

@@ -9,7 +9,8 @@
 //        chem[bin][NCHEM]   (k1..k58, ncr*, k13dd*14)      600 x 48 doubles = 230 KB
 //        cool[bin][NCOOL]   (ceHI..brem, GA*, H2LTE, ...)  600 x 24 doubles = 115 KB
 //    so the two bins a cell interpolates between are ONE contiguous span
-//    (2 x 384 B resp. 2 x 192 B, fetched as double2) instead of 92 scattered 8-byte gathers.
+//    (2 x 384 B resp. 2 x 192 B) instead of 92 scattered 8-byte gathers; in the solve kernel a
+//    group of lanes reads that span coalesced (one double2 piece per lane).
 //  * h2dust[dustbin][bin] (1.2 MB) and the Cloudy grids stay in the reference's
 //    order (T fastest) and are read through the read-only path (L2-resident).
 #ifndef GRB200_DEVICE_H
@@ -18,18 +19,21 @@
 #include <cstdint>
 
 // column indices of the packed chemistry-rate matrix.  A row is 48 doubles = 384 B = three
-// 128-byte lines; column groups start on even columns so they can be fetched as double2.
+// 128-byte lines: columns [0,32) are the rates every subcycle needs (two lines), columns
+// [32,46) the 14 Martin+96 coefficients of the density-dependent k13 (one line).  The solve
+// kernel fetches a cell's two adjacent rows warp-cooperatively (kernels.cu: coop_fetch), a
+// group of lanes reading one cell's row pair as consecutive double2 pieces.
 enum {
-  C_K1 = 0, C_K2, C_K3, C_K4, C_K5, C_K6, C_K57, C_K58,          // 6-species network
-  C_K7, C_K8, C_K9, C_K10, C_K11, C_K12, C_K13, C_K14, C_K15,    // + H2
-  C_K16, C_K17, C_K18, C_K19, C_K22, C_NCRN, C_NCRD1, C_NCRD2,
-  C_PAD0,
-  C_K13DD0,                                                       // 14 columns
-  C_K50 = C_K13DD0 + 14, C_K51, C_K52, C_K53, C_K54, C_K55, C_K56,  // + D
-  C_PAD1,
+  C_k1 = 0, C_k2, C_k3, C_k4, C_k5, C_k6, C_k57, C_k58,          // 6-species network  [0,8)
+  C_k7, C_k8, C_k9, C_k10, C_k11, C_k12, C_k13, C_k14, C_k15,    // + H2              [8,25)
+  C_k16, C_k17, C_k18, C_k19, C_k22, C_ncrn, C_ncrd1, C_ncrd2,
+  C_k50, C_k51, C_k52, C_k53, C_k54, C_k55, C_k56,               // + D               [25,32)
+  C_K13DD0,                                                       // 14 columns        [32,46)
+  C_PAD0 = C_K13DD0 + 14, C_PAD1,
   NCHEM
 };
-static_assert(NCHEM == 48 && C_K13DD0 == 26 && C_K50 == 40, "packed chemistry row is 48 doubles");
+static_assert(NCHEM == 48 && C_K13DD0 == 32 && C_k50 == 25, "packed chemistry row is 48 doubles");
+#define GRB_NCHEM_MAIN 32
 
 // column indices of the packed cooling-rate matrix (24 doubles = 192 B per row)
 enum {

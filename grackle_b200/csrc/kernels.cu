@@ -224,12 +224,13 @@ struct SubState {           // per-cell carry between subcycles
   int iter;
 };
 
-// One subcycle of solve_rate_cool_g.F:451-817 for one cell, in three stages so that the
-// warps of a CTA can be re-aligned between them (see k_solve): (a) cool_rate, (b) the rate
-// lookup, (c) rate-limited dt, energy update and the species sweep.  subcycle_finish returns
-// true when the cell has reached dt.
+// One subcycle of solve_rate_cool_g.F:451-817 for one cell is split into per-cell stages
+// with the warp-cooperative table fetches between them (see k_solve): thermo_head, [fetch
+// A], cool_sums + k13_martin, [fetch B], subcycle_lookup, subcycle_finish (rate-limited dt,
+// energy update, species sweep).  subcycle_finish returns true when the cell has reached dt.
 template <int PC>
-__device__ __forceinline__ void subcycle_lookup(const GrParams &P, const Cell &c, const Thermo &th, size_t x, const Rates &r)
+__device__ __forceinline__ void subcycle_lookup(const GrParams &P, const Cell &c, const Thermo &th, size_t x,
+                                                const TIndex &ti, double k13dd, const Rates &r)
 {
   Neigh nb;
   if (PC > 1 && P.iH2shield == 1) {
@@ -239,12 +240,12 @@ __device__ __forceinline__ void subcycle_lookup(const GrParams &P, const Cell &c
     nb.d[0] = D[x + 1] * sc; nb.d[1] = D[x - 1] * sc; nb.d[2] = D[x + sj] * sc;
     nb.d[3] = D[x - sj] * sc; nb.d[4] = D[x + sk] * sc; nb.d[5] = D[x - sk] * sc;
   }
-  lookup_rates<PC>(P, c, th, nb, r);
+  lookup_rates<PC>(P, c, th, nb, ti, k13dd, r);
 }
 
 template <int PC>
 __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubState &s, const Thermo &th,
-                                                const Rates &r)
+                                                const TIndex &ti, const Rates &r)
 {
   const double dt = P.dt;
   double dtit = GRB_HUGE8;
@@ -270,16 +271,17 @@ __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubS
     if (PC > 1 && c.d * P.dom > 1e8 && edot > 0.0) {
       // keep the 3-body equilibrium H abundance from changing by more than 10 %
       const double fd = P.fh * c.d;
-      const int ridx = (int)RK(idx);
+      const int ridx = ti.idx;
+      const double lt1 = (P.logtem0 + (ridx - 1) * P.dlogtem), lt2 = (P.logtem0 + (ridx) * P.dlogtem);   // = t_index
       const double k22lo = ld(P.k22a + ridx - 1), k22hi = ld(P.k22a + ridx);
       const double k13lo = ld(P.k13a + ridx - 1), k13hi = ld(P.k13a + ridx);
-      const double eqt2 = dmin(th.logtgas + 0.1 * P.dlogtem, RK(t2));
-      double eqtdef = (eqt2 - RK(t1)) / (RK(t2) - RK(t1));
+      const double eqt2 = dmin(th.logtgas + 0.1 * P.dlogtem, lt2);
+      double eqtdef = (eqt2 - lt1) / (lt2 - lt1);
       const double eqk222 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk132 = k13lo + (k13hi - k13lo) * eqtdef;
       const double heq2 = (-1.0 / (4.0 * eqk222)) * (eqk132 - sqrt(8.0 * eqk132 * eqk222 * fd + eqk132 * eqk132));
-      const double eqt1 = dmax(th.logtgas - 0.1 * P.dlogtem, RK(t1));
-      eqtdef = (eqt1 - RK(t1)) / (RK(t2) - RK(t1));
+      const double eqt1 = dmax(th.logtgas - 0.1 * P.dlogtem, lt1);
+      eqtdef = (eqt1 - lt1) / (lt2 - lt1);
       const double eqk221 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk131 = k13lo + (k13hi - k13lo) * eqtdef;
       const double heq1 = (-1.0 / (4.0 * eqk221)) * (eqk131 - sqrt(8.0 * eqk131 * eqk221 * fd + eqk131 * eqk131));
@@ -345,25 +347,19 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 
 // CTA-wide re-alignment points.  The executed path of one subcycle is ~100 KB of SASS,
 // three times the SM's 32 KB instruction cache; warps that drift apart each stream it from
-// L2 on their own (ncu round 1: 55 % of all stall cycles were stall_no_inst).  Barriers
-// between the stages keep the warps of a CTA inside the same few KB of code, so one warp's
-// fetch serves all of them.
+// L2 on their own (ncu round 1: 55 % of all stall cycles were stall_no_inst).  A barrier per
+// subcycle keeps the warps of a group inside the same few KB of code, so one warp's fetch
+// serves all of them.
 // The CTA is split into lockstep groups of GRB_GROUP_WARPS warps, each on its own named
 // barrier: inside a group one warp's instruction fetch serves all, while the groups run out
 // of phase with each other so one group's barrier tail is covered by the others' work.
-#ifndef GRB_STAGE_BARRIERS
-#define GRB_STAGE_BARRIERS 0      /* extra re-alignment points inside a subcycle (measured: 0 is fastest) */
-#endif
 #ifndef GRB_GROUP_WARPS
 #define GRB_GROUP_WARPS 8
 #endif
+
 static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0, "CTA must be whole lockstep groups");
 static_assert(GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15, "named barriers 1..15");
 
-__device__ __forceinline__ void group_align(int bar_id)
-{
-  asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(32 * GRB_GROUP_WARPS) : "memory");
-}
 // barrier + OR-reduction of a predicate over the group
 __device__ __forceinline__ bool group_any(int bar_id, bool pred)
 {
@@ -376,14 +372,55 @@ __device__ __forceinline__ bool group_any(int bar_id, bool pred)
   return out != 0;
 }
 
+// Warp-cooperative fetch of one table segment for the 32 cells a warp owns.
+//   table   first column of the segment in row 0 (16-byte aligned)
+//   ROWB    bytes per table row
+//   my_off  THIS lane's cell: byte offset of its lower row; my_t: its interpolation weight
+//   dst0    this warp's lane-0 slot row + the segment's first slot
+// G lanes serve one cell per pass (32/G cells per pass, G passes): lane g < NP of a group
+// loads the double2 piece g of the cell's lower and upper row - the group's loads are
+// consecutive 16-byte words of one or two 128-byte lines - interpolates a + (b - a) * t
+// (solve_rate_cool_g.F:1225-1320, cool1d_multi_g.F:387-410) and stores columns 2g / 2g+1 to
+// slots g / NP+g of that cell's row.  All 2*G loads are independent, so the compiler keeps
+// as many in flight as registers allow.
+template <int G, int NP, int ROWB>
+__device__ __forceinline__ void coop_fetch(const double *table, int my_off, double my_t, double *dst0)
+{
+  static_assert(G == 4 || G == 8 || G == 16, "lanes per cell");
+  static_assert(NP <= G, "pieces per cell");
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int g = lane & (G - 1), sub = lane / G;
+  constexpr int CPP = 32 / G;      // cells per pass
+  const char *src = reinterpret_cast<const char *>(table) + 16 * g;
+  double *dst = dst0 + sub * GRB_SLOT_STRIDE + g;
+  // (explicit load batches of 2/4/8 passes and a group barrier only every 2nd/4th subcycle
+  // were measured slower than this plain loop: 12.2/11.9/11.6 and 10.9/9.5 vs 12.6 Mcell/s)
+#pragma unroll
+  for (int pass = 0; pass < G; pass++) {
+    const int cell = pass * CPP + sub;
+    const int off = __shfl_sync(full, my_off, cell);
+    const double t = __shfl_sync(full, my_t, cell);
+    if (NP == G || g < NP) {
+      const double2 a = __ldg(reinterpret_cast<const double2 *>(src + off));
+      const double2 b = __ldg(reinterpret_cast<const double2 *>(src + off + ROWB));
+      dst[pass * CPP * GRB_SLOT_STRIDE] = a.x + (b.x - a.x) * t;
+      dst[pass * CPP * GRB_SLOT_STRIDE + NP] = a.y + (b.y - a.y) * t;
+    }
+  }
+}
+
 template <int PC>
 __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P)
 {
-  extern __shared__ double rate_slots[];     // [NRATES][GRB_SOLVE_THREADS]
-  const Rates r{rate_slots + threadIdx.x};
+  extern __shared__ double slot_rows[];     // [GRB_SOLVE_THREADS][GRB_SLOT_STRIDE]
+  double *const my_slots = slot_rows + (size_t)threadIdx.x * GRB_SLOT_STRIDE;
+  double *const warp_slots = slot_rows + (size_t)(threadIdx.x & ~31u) * GRB_SLOT_STRIDE;
+  const Rates r{my_slots};
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int bar_id = 1 + (int)(threadIdx.x >> 5) / GRB_GROUP_WARPS;
+  const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
   Cell c;
   SubState s;
   size_t x = 0;
@@ -419,23 +456,53 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
     }
     // after the refill every lane either owns a cell or has seen the end of the queue
     if (!group_any(bar_id, active)) break;
+
     // ---- one subcycle on every busy lane ----
+    // stage 1 (per cell): temperature and the two log-T bins.  Idle lanes point at bin 1.
     Thermo th;
+    TIndex tb;                       // bin of ln(tgas): chemistry rows
+    tb.idx = 1; tb.tdef = 0.0; tb.t1 = tb.t2 = 0.0;
+    int offA = 0, offB = 0;          // byte offsets of the lower rows (cooling, chemistry)
+    double tdefA = 0.0, logtem = 0.0;
     if (active) {
       load_extras<PC>(P, x, c);
-      cool_rate<PC>(P, c, s.iter == 1, s.tgasold, th);
+      logtem = thermo_head<PC>(P, c, s.iter == 1, s.tgasold, th, true);
+      if ((PC > 0) || (P.idustall > 0)) {           // cool1d_multi_g.F:349-357
+        const TIndex ta = t_index(P, logtem);
+        offA = (ta.idx - 1) * (NCOOL * 8);
+        tdefA = ta.tdef;
+      }
+      if (PC > 0) {                                 // solve_rate_cool_g.F:1211-1222
+        double lt = dmax(th.logtgas, P.logtem0);
+        lt = dmin(lt, P.logtem9);
+        tb = t_index(P, lt);
+        offB = (tb.idx - 1) * (NCHEM * 8);
+      }
     }
-#if GRB_STAGE_BARRIERS >= 2
-    group_align(bar_id);
-#endif
+    // stage 2 (warp): cooling rows and the k13dd coefficients -> slots
+    if (PC > 0) coop_fetch<8, 8, NCOOL * 8>(P.cool, offA, tdefA, warp_slots + SLA_COOL0);
+    if (PC > 1 || anydust) coop_fetch<4, 4, NCOOL * 8>(P.cool + 16, offA, tdefA, warp_slots + SLA_COOL1);
+    if (PC > 1 && P.ithreebody == 0)
+      coop_fetch<8, 7, NCHEM * 8>(P.chem + C_K13DD0, offB, tb.tdef, warp_slots + SLA_DD);
+    __syncwarp();
+    // stage 3 (per cell): cooling / heating sums, density-dependent k13
+    double k13dd = GRB_TINY8;
+    if (active) {
+      cool_sums<PC>(P, c, logtem, CoolSlots{my_slots}, s.tgasold, th);
+      if (PC > 1 && P.ithreebody == 0) k13dd = k13_martin(P, c, th, my_slots);
+    }
+    __syncwarp();
     if (PC > 0) {
-      if (active) subcycle_lookup<PC>(P, c, th, x, r);
-#if GRB_STAGE_BARRIERS >= 1
-      group_align(bar_id);
-#endif
+      // stage 4 (warp): chemistry rows -> slots
+      if (PC == 1) coop_fetch<4, 4, NCHEM * 8>(P.chem, offB, tb.tdef, warp_slots);
+      else if (PC == 2) coop_fetch<16, 13, NCHEM * 8>(P.chem, offB, tb.tdef, warp_slots);
+      else coop_fetch<16, 16, NCHEM * 8>(P.chem, offB, tb.tdef, warp_slots);
+      __syncwarp();
+      // stage 5 (per cell): shielding, H2 on dust
+      if (active) subcycle_lookup<PC>(P, c, th, x, tb, k13dd, r);
     }
     if (active) {
-      const bool done = subcycle_finish<PC>(P, c, s, th, r);
+      const bool done = subcycle_finish<PC>(P, c, s, th, tb, r);
       my_sub++;
       if (done || s.iter >= P.itmax) {
         if (!done) my_itmax++;
@@ -447,6 +514,7 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
         s.iter++;
       }
     }
+    __syncwarp();
   }
 
   // ---- diagnostics: warp reduce, one atomic per warp ----
@@ -488,7 +556,7 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double *sink, int iters, doub
 // ------------------------------------------------------------------------------
 // host-callable launchers (declared in gr_launch.h)
 // ------------------------------------------------------------------------------
-#define GRB_SOLVE_SMEM ((size_t)NRATES * GRB_SOLVE_THREADS * sizeof(double))
+#define GRB_SOLVE_SMEM ((size_t)GRB_SLOT_STRIDE * GRB_SOLVE_THREADS * sizeof(double))
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 }  // namespace grb

@@ -8,114 +8,87 @@
 
 namespace grb {
 
-// The rates of one cell-subcycle live in SHARED memory between the lookup and the species
-// update (slot-major: slot i of thread t at base[i*GRB_SOLVE_THREADS + t], conflict-free),
-// which takes ~90 registers off the solve kernel.  Rates is a view of one thread's column.
-enum {
-  RI_k1,
-  RI_k2,
-  RI_k3,
-  RI_k4,
-  RI_k5,
-  RI_k6,
-  RI_k57,
-  RI_k58,
-  RI_k7,
-  RI_k8,
-  RI_k9,
-  RI_k10,
-  RI_k11,
-  RI_k12,
-  RI_k13,
-  RI_k14,
-  RI_k15,
-  RI_k16,
-  RI_k17,
-  RI_k18,
-  RI_k19,
-  RI_k22,
-  RI_ncrn,
-  RI_ncrd1,
-  RI_ncrd2,
-  RI_k50,
-  RI_k51,
-  RI_k52,
-  RI_k53,
-  RI_k54,
-  RI_k55,
-  RI_k56,
-  RI_h2dust,
-  RI_k24s,
-  RI_k25s,
-  RI_k26s,
-  RI_k28s,
-  RI_k29s,
-  RI_k30s,
-  RI_k31s,
-  RI_t1,
-  RI_t2,
-  RI_idx,          // log-T bin of the lookup (stored as a double)
-  NRATES
-};
+// The interpolated rates of one cell-subcycle live in SHARED memory (a row of GRB_SLOT_STRIDE
+// doubles per thread; the odd stride makes a warp's accesses to one slot conflict-free).  The
+// rows are FILLED warp-cooperatively (kernels.cu: coop_fetch): a group of G lanes reads one
+// cell's two adjacent table rows as consecutive double2 pieces - coalesced, one L1 wavefront
+// per 128-byte line instead of one per lane - interpolates, and stores into that cell's row.
+// Piece g of a segment of NP pieces holds columns (2g, 2g+1); they land in slots
+// base+g and base+NP+g so that the lanes of a group store to consecutive words.
+//
+// Slot map.  Phase A (before the cooling sums): cooling columns [0,16) -> slots [0,16),
+// cooling columns [16,24) -> [16,24), the 14 k13dd columns -> [24,38).  Phase B (before the
+// species update) overwrites them: chemistry columns [0,32) -> slots [0,32), then the slots
+// the lookup itself produces.
+#define GRB_SLOT_STRIDE 41
+enum { SL_h2dust = GRB_NCHEM_MAIN, SL_k24s, SL_k25s, SL_k26s, SL_k28s, SL_k29s, SL_k30s, SL_k31s, NSLOT };
+static_assert(NSLOT <= GRB_SLOT_STRIDE && (GRB_SLOT_STRIDE & 1) == 1, "slot row");
+enum { SLA_COOL0 = 0, SLA_COOL1 = 16, SLA_DD = 24 };
+
+// pieces of the chemistry row the network PC needs every subcycle
+__host__ __device__ constexpr int chem_pieces(int pc) { return pc == 1 ? 4 : (pc == 2 ? 13 : 16); }
+template <int PC>
+__host__ __device__ constexpr int chem_slot(int col) { return (col >> 1) + (col & 1) * chem_pieces(PC); }
+__host__ __device__ constexpr int cool_slot(int col)
+{
+  return col < 16 ? SLA_COOL0 + (col >> 1) + (col & 1) * 8 : SLA_COOL1 + ((col - 16) >> 1) + (col & 1) * 4;
+}
+__host__ __device__ constexpr int dd_slot(int n) { return SLA_DD + (n >> 1) + (n & 1) * 7; }
+static_assert(2 * chem_pieces(1) > C_k58 && 2 * chem_pieces(2) > C_ncrd2 && 2 * chem_pieces(3) > C_k56, "chem pieces");
+
 struct Rates {
-  double *base;    // shared memory, already offset by threadIdx.x
+  double *base;    // this thread's slot row in shared memory
 };
-#define RK(name) (r.base[RI_##name * GRB_SOLVE_THREADS])
-static_assert(RI_k58 - RI_k1 == C_K58 - C_K1 && RI_k16 - RI_k7 == C_K16 - C_K7 &&
-              RI_ncrd2 - RI_k17 == C_NCRD2 - C_K17 && RI_k56 - RI_k50 == C_K56 - C_K50,
-              "rate slots must follow the packed column order");
+#define RK(name) (r.base[chem_slot<PC>(C_##name)])
+#define RS(name) (r.base[SL_##name])
+// cooling-table values read back from the slots (phase A)
+struct CoolSlots {
+  const double *base;
+  __device__ __forceinline__ double operator()(int col) const { return base[cool_slot(col)]; }
+};
 
 // neighbour densities for the Sobolev-like H2 shielding length (H2_self_shielding == 1)
 struct Neigh { double d[6]; };
 
 // ---------------------------------------------------------------------------------
-// lookup_cool_rates1d_g (solve_rate_cool_g.F:1079-1737)
+// lookup_cool_rates1d_g (solve_rate_cool_g.F:1079-1737).  The plain log-T interpolations
+// (:1225-1320) are done by coop_fetch; this is everything else, per cell.
+// k13_martin: the density-dependent H2 collisional dissociation rate (Martin+96, :1709-1733)
+// from the 14 interpolated coefficients `dd` (phase A slots).
 // ---------------------------------------------------------------------------------
+__device__ inline double k13_martin(const GrParams &P, const Cell &c, const Thermo &th, const double *slots)
+{
+  const double nh = dmin(c.HI * P.dom, 1.0e9);
+  double k13 = GRB_TINY8;
+  if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
+#define DD(n) (slots[dd_slot(n)])
+    double cid = DD(0) - DD(1) / (1.0 + pow_pos(nh / DD(4), DD(6))) + DD(2) -
+                 DD(3) / (1.0 + pow_pos(nh / DD(5), DD(6)));
+    cid = dmax(exp10(cid), GRB_TINY8);
+    double dtn = DD(7) - DD(8) / (1.0 + pow_pos(nh / DD(11), DD(13))) + DD(9) -
+                 DD(10) / (1.0 + pow_pos(nh / DD(12), DD(13)));
+    dtn = dmax(exp10(dtn), GRB_TINY8);
+    k13 = dtn + cid;
+#undef DD
+  }
+  return k13;
+}
+
+// ti = the log-T bin of ln(tgas) (the one the chemistry rows were fetched at)
 template <int PC>
 __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Thermo &th,
-                                    const Neigh &nb, const Rates &r)
+                                    const Neigh &nb, const TIndex &ti, double k13dd, const Rates &r)
 {
   const bool anydust = (P.idust > 0) || (P.idustall > 0);
   const double dom = P.dom;
-  double logtem = th.logtgas;          // = log(th.tgas), formed in cool_rate
-  logtem = dmax(logtem, P.logtem0);
-  logtem = dmin(logtem, P.logtem9);
-  const TIndex ti = t_index(P, logtem);
-  RK(idx) = (double)ti.idx; RK(t1) = ti.t1; RK(t2) = ti.t2;
   const double tdef = ti.tdef;
-  const double *row = P.chem + (size_t)(ti.idx - 1) * NCHEM;
-#define K_LERP(col) lerp_row(row, NCHEM, col, tdef)
-
-  // slots RI_k1.. follow the column order of the packed row, so a column group lands in
-  // consecutive slots
-  {
-    double v[8];
-    lerp_cols<NCHEM, C_K1, 8>(row, tdef, v);
-#pragma unroll
-    for (int i = 0; i < 8; i++) r.base[(RI_k1 + i) * GRB_SOLVE_THREADS] = v[i];
-  }
-  if (PC > 1) {
-    double v[10];
-    lerp_cols<NCHEM, C_K7, 10>(row, tdef, v);                 // k7 .. k16
-#pragma unroll
-    for (int i = 0; i < 10; i++) r.base[(RI_k7 + i) * GRB_SOLVE_THREADS] = v[i];
-    double w[8];
-    lerp_cols<NCHEM, C_K17, 8>(row, tdef, w);                 // k17 k18 k19 k22 ncr_n ncr_d1 ncr_d2 (pad)
-#pragma unroll
-    for (int i = 0; i < 7; i++) r.base[(RI_k17 + i) * GRB_SOLVE_THREADS] = w[i];
-  }
-  if (PC > 2) {
-    double v[8];
-    lerp_cols<NCHEM, C_K50, 8>(row, tdef, v);                 // k50 .. k56 (pad)
-#pragma unroll
-    for (int i = 0; i < 7; i++) r.base[(RI_k50 + i) * GRB_SOLVE_THREADS] = v[i];
-  }
+  if (PC > 1 && P.ithreebody == 0) RK(k13) = k13dd;
 
   // H2 formation on grains: bilinear in (ln T, ln T_dust) (:1327-1378)
-  RK(h2dust) = 0.0;
+  RS(h2dust) = 0.0;
   if (anydust) {
     if (th.tdust > P.dtemend) {
-      RK(h2dust) = GRB_TINY8;
+      RS(h2dust) = GRB_TINY8;
     } else {
       double dl = log(th.tdust);
       dl = dmax(dl, P.d_logtem0);
@@ -128,16 +101,16 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
       const double *c2 = c1 + P.nratec;
       const double dusti1 = ld(c1) + (ld(c1 + 1) - ld(c1)) * tdef;
       const double dusti2 = ld(c2) + (ld(c2 + 1) - ld(c2)) * tdef;
-      RK(h2dust) = dusti1 + (dusti2 - dusti1) * d_tdef;
-      RK(h2dust) = RK(h2dust) * th.dust2gas;
+      RS(h2dust) = dusti1 + (dusti2 - dusti1) * d_tdef;
+      RS(h2dust) = RS(h2dust) * th.dust2gas;
     }
   }
 
-  RK(k24s) = P.k24; RK(k25s) = P.k25; RK(k26s) = P.k26; RK(k28s) = P.k28; RK(k29s) = P.k29; RK(k30s) = P.k30;
-  RK(k31s) = 0.0;
+  RS(k24s) = P.k24; RS(k25s) = P.k25; RS(k26s) = P.k26; RS(k28s) = P.k28; RS(k29s) = P.k29; RS(k30s) = P.k30;
+  RS(k31s) = 0.0;
 
   if (PC > 1) {     // H2 self-shielding, Wolcott-Green & Haiman (2019) (:1397-1490)
-    RK(k31s) = (P.iradtrans == 0) ? P.k31 : P.k31 + c.kdissH2I;
+    RS(k31s) = (P.iradtrans == 0) ? P.k31 : P.k31 + c.kdissH2I;
     if (P.iH2shield > 0) {
       double l_H2shield;
       if (P.iH2shield == 1) {
@@ -167,9 +140,9 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
       double f_shield = 0.965 / pow_pos(1.0 + x / b_doppler, aWG) +
                         0.035 * exp(-8.5e-4 * sqrt(1.0 + x)) / sqrt(1.0 + x);
       f_shield = dmin(f_shield, 1.0);
-      RK(k31s) = f_shield * RK(k31s);
+      RS(k31s) = f_shield * RS(k31s);
     }
-    if (P.iH2shieldcustom > 0) RK(k31s) = c.fshield * RK(k31s);
+    if (P.iH2shieldcustom > 0) RS(k31s) = c.fshield * RS(k31s);
   }
 
   if (P.iradshield > 0) {   // UVB self-shielding (:1492-1676)
@@ -183,35 +156,18 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
     const double fH = rahmati_f(nratio);
     nratio = 0.25 * (c.HeI + c.HeII + c.HeIII) * dom / (P.ssh_sig_hei * tfac * P.ssh_k26);
     const double fHe = rahmati_f(nratio);
-    RK(k24s) = (P.k24 < GRB_TINY8) ? 0.0 : RK(k24s) * fH;
-    RK(k29s) = (P.k29 < GRB_TINY8) ? 0.0 : RK(k29s) * fH;
+    RS(k24s) = (P.k24 < GRB_TINY8) ? 0.0 : RS(k24s) * fH;
+    RS(k29s) = (P.k29 < GRB_TINY8) ? 0.0 : RS(k29s) * fH;
     if (P.iradshield == 1) {
-      RK(k25s) = P.k25; RK(k26s) = P.k26;
+      RS(k25s) = P.k25; RS(k26s) = P.k26;
     } else if (P.iradshield == 2 || P.iradshield == 3) {
-      RK(k26s) = (P.k26 < GRB_TINY8) ? 0.0 : RK(k26s) * fHe;
-      RK(k28s) = (P.k28 < GRB_TINY8) ? 0.0 : RK(k28s) * fHe;
-      RK(k30s) = (P.k30 < GRB_TINY8) ? 0.0 : RK(k30s) * fHe;
-      RK(k25s) = (P.iradshield == 2) ? P.k25 : 0.0;
+      RS(k26s) = (P.k26 < GRB_TINY8) ? 0.0 : RS(k26s) * fHe;
+      RS(k28s) = (P.k28 < GRB_TINY8) ? 0.0 : RS(k28s) * fHe;
+      RS(k30s) = (P.k30 < GRB_TINY8) ? 0.0 : RS(k30s) * fHe;
+      RS(k25s) = (P.iradshield == 2) ? P.k25 : 0.0;
     }
   }
 
-  // density-dependent collisional dissociation of H2 (Martin+96) (:1709-1733)
-  if (PC > 1 && P.ithreebody == 0) {
-    const double nh = dmin(c.HI * dom, 1.0e9);
-    RK(k13) = GRB_TINY8;
-    if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
-      double dd[14];
-      lerp_cols<NCHEM, C_K13DD0, 14>(row, tdef, dd);
-      double cid = dd[0] - dd[1] / (1.0 + pow_pos(nh / dd[4], dd[6])) + dd[2] -
-                   dd[3] / (1.0 + pow_pos(nh / dd[5], dd[6]));
-      cid = dmax(exp10(cid), GRB_TINY8);
-      double dtn = dd[7] - dd[8] / (1.0 + pow_pos(nh / dd[11], dd[13])) + dd[9] -
-                   dd[10] / (1.0 + pow_pos(nh / dd[12], dd[13]));
-      dtn = dmax(exp10(dtn), GRB_TINY8);
-      RK(k13) = dtn + cid;
-    }
-  }
-#undef K_LERP
 }
 
 // ---------------------------------------------------------------------------------
@@ -228,8 +184,8 @@ __device__ inline void rate_derivs(const GrParams &P, const Cell &c, const Therm
     dedot = + RK(k1) * HI * de + RK(k3) * HeI * de / 4.0 + RK(k5) * HeII * de / 4.0
             - RK(k2) * HII * de - RK(k4) * HeII * de / 4.0 - RK(k6) * HeIII * de / 4.0
             + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0
-            + (RK(k24s) * HI + RK(k25s) * HeII / 4.0 + RK(k26s) * HeI / 4.0);
-    HIdot = - RK(k1) * HI * de + RK(k2) * HII * de - RK(k57) * HI * HI - RK(k58) * HI * HeI / 4.0 - RK(k24s) * HI;
+            + (RS(k24s) * HI + RS(k25s) * HeII / 4.0 + RS(k26s) * HeI / 4.0);
+    HIdot = - RK(k1) * HI * de + RK(k2) * HII * de - RK(k57) * HI * HI - RK(k58) * HI * HeI / 4.0 - RS(k24s) * HI;
   } else {
     const double HM = c.HM, H2I = c.H2I, H2II = c.H2II;
     HIdot = - RK(k1) * de * HI - RK(k7) * de * HI - RK(k8) * HM * HI - RK(k9) * HII * HI
@@ -238,22 +194,22 @@ __device__ inline void rate_derivs(const GrParams &P, const Cell &c, const Therm
             + RK(k11) * HII * H2I / 2.0 + 2.0 * RK(k12) * de * H2I / 2.0
             + RK(k14) * HM * de + RK(k15) * HM * HI + 2.0 * RK(k16) * HM * HII
             + 2.0 * RK(k18) * H2II * de / 2.0 + RK(k19) * H2II * HM / 2.0
-            - RK(k57) * HI * HI - RK(k58) * HI * HeI / 4.0 - RK(k24s) * HI
-            + 2.0 * RK(k31s) * H2I / 2.0;
-    if (anydust) HIdot = HIdot - 2.0 * RK(h2dust) * th.rhoH;
+            - RK(k57) * HI * HI - RK(k58) * HI * HeI / 4.0 - RS(k24s) * HI
+            + 2.0 * RS(k31s) * H2I / 2.0;
+    if (anydust) HIdot = HIdot - 2.0 * RS(h2dust) * th.rhoH;
 
     dedot = + RK(k1) * HI * de + RK(k3) * HeI * de / 4.0 + RK(k5) * HeII * de / 4.0
             + RK(k8) * HM * HI + RK(k15) * HM * HI + RK(k17) * HM * HII + RK(k14) * HM * de
             - RK(k2) * HII * de - RK(k4) * HeII * de / 4.0 - RK(k6) * HeIII * de / 4.0
             - RK(k7) * HI * de - RK(k18) * H2II * de / 2.0
             + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0
-            + (RK(k24s) * HI + RK(k25s) * HeII / 4.0 + RK(k26s) * HeI / 4.0);
+            + (RS(k24s) * HI + RS(k25s) * HeII / 4.0 + RS(k26s) * HeI / 4.0);
 
     // H2 formation heating, Omukai (2000) eq. 23
     const double h2heatfac = 1.0 / (1.0 + (RK(ncrn) / (P.dom * (HI * RK(ncrd1) + H2I * 0.5 * RK(ncrd2)))));
     double H2delta = HI * (4.48 * RK(k22) * (HI * HI) - 4.48 * RK(k13) * H2I / 2.0);
     if (H2delta > 0.0) H2delta = H2delta * h2heatfac;
-    if (anydust) H2delta = H2delta + RK(h2dust) * HI * th.rhoH * (0.2 + 4.2 * h2heatfac);
+    if (anydust) H2delta = H2delta + RS(h2dust) * HI * th.rhoH * (0.2 + 4.2 * h2heatfac);
     edot = edot + P.chunit * H2delta * 1.0;
   }
   if (P.iradtrans == 1) {
@@ -285,11 +241,11 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
 
   if (PC == 1) {
     scoef = RK(k2) * HII * de;
-    acoef = RK(k1) * de + RK(k57) * HI + RK(k58) * HeI / 4.0 + RK(k24s);
+    acoef = RK(k1) * de + RK(k57) * HI + RK(k58) * HeI / 4.0 + RS(k24s);
     if (rt) acoef = acoef + kphHI;
     HIp = (scoef * dt + HI) / (1.0 + acoef * dt);
 
-    scoef = RK(k1) * HIp * de + RK(k57) * HIp * HIp + RK(k58) * HIp * HeI / 4.0 + RK(k24s) * HIp;
+    scoef = RK(k1) * HIp * de + RK(k57) * HIp * HIp + RK(k58) * HIp * HeI / 4.0 + RS(k24s) * HIp;
     if (rt) scoef = scoef + kphHI * HIp;
     acoef = RK(k2) * de;
     HIIp = (scoef * dt + HII) / (1.0 + acoef * dt);
@@ -298,17 +254,17 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
 
   // helium, every network
   scoef = RK(k4) * HeII * de;
-  acoef = RK(k3) * de + RK(k26s);
+  acoef = RK(k3) * de + RS(k26s);
   if (rt_all) acoef = acoef + kphHeI;
   const double HeIp = (scoef * dt + HeI) / (1.0 + acoef * dt);
 
-  scoef = RK(k3) * HeIp * de + RK(k6) * HeIII * de + RK(k26s) * HeIp;
+  scoef = RK(k3) * HeIp * de + RK(k6) * HeIII * de + RS(k26s) * HeIp;
   if (rt_all) scoef = scoef + kphHeI * HeIp;
-  acoef = RK(k4) * de + RK(k5) * de + RK(k25s);
+  acoef = RK(k4) * de + RK(k5) * de + RS(k25s);
   if (rt_all) acoef = acoef + kphHeII;
   const double HeIIp = (scoef * dt + HeII) / (1.0 + acoef * dt);
 
-  scoef = RK(k5) * HeIIp * de + RK(k25s) * HeIIp;
+  scoef = RK(k5) * HeIIp * de + RS(k25s) * HeIIp;
   if (rt_all) scoef = scoef + kphHeII * HeIIp;
   acoef = RK(k6) * de;
   const double HeIIIp = (scoef * dt + HeIII) / (1.0 + acoef * dt);
@@ -318,21 +274,21 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
     scoef = RK(k2) * HII * de + 2.0 * RK(k13) * HI * H2I / 2.0 + RK(k11) * HII * H2I / 2.0 +
             2.0 * RK(k12) * de * H2I / 2.0 + RK(k14) * HM * de + RK(k15) * HM * HI +
             2.0 * RK(k16) * HM * HII + 2.0 * RK(k18) * H2II * de / 2.0 + RK(k19) * H2II * HM / 2.0 +
-            2.0 * RK(k31s) * H2I / 2.0;
+            2.0 * RS(k31s) * H2I / 2.0;
     acoef = RK(k1) * de + RK(k7) * de + RK(k8) * HM + RK(k9) * HII + RK(k10) * H2II / 2.0 +
-            2.0 * RK(k22) * (HI * HI) + RK(k57) * HI + RK(k58) * HeI / 4.0 + RK(k24s);
+            2.0 * RK(k22) * (HI * HI) + RK(k57) * HI + RK(k58) * HeI / 4.0 + RS(k24s);
     if (rt) acoef = acoef + kphHI;
-    if (anydust) acoef = acoef + 2.0 * RK(h2dust) * th.rhoH;
+    if (anydust) acoef = acoef + 2.0 * RS(h2dust) * th.rhoH;
     HIp = (scoef * dt + HI) / (1. + acoef * dt);
 
     scoef = RK(k1) * HI * de + RK(k10) * H2II * HI / 2.0 + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0 +
-            RK(k24s) * HI;
+            RS(k24s) * HI;
     if (rt) scoef = scoef + kphHI * HI;
     acoef = RK(k2) * de + RK(k9) * HI + RK(k11) * H2I / 2.0 + RK(k16) * HM + RK(k17) * HM;
     HIIp = (scoef * dt + HII) / (1.0 + acoef * dt);
 
     scoef = RK(k8) * HM * HI + RK(k15) * HM * HI + RK(k17) * HM * HII + RK(k57) * HI * HI +
-            RK(k58) * HI * HeI / 4.0 + RK(k24s) * HIp + RK(k25s) * HeIIp / 4.0 + RK(k26s) * HeIp / 4.0;
+            RK(k58) * HI * HeI / 4.0 + RS(k24s) * HIp + RS(k25s) * HeIIp / 4.0 + RS(k26s) * HeIp / 4.0;
     if (rt_all) scoef = scoef + kphHI * HIp + kphHeI * HeIp / 4.0 + kphHeII * HeIIp / 4.0;
     if (rt_honly) scoef = scoef + kphHI * HIp;
     acoef = -(RK(k1) * HI - RK(k2) * HII + RK(k3) * HeI / 4.0 - RK(k6) * HeIII / 4.0 + RK(k5) * HeII / 4.0 -
@@ -341,8 +297,8 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
 
     scoef = 2.0 * (RK(k8) * HM * HI + RK(k10) * H2II * HI / 2.0 + RK(k19) * H2II * HM / 2.0 +
                    RK(k22) * HI * (HI * HI));
-    acoef = (RK(k13) * HI + RK(k11) * HII + RK(k12) * de) + RK(k29s) + RK(k31s);
-    if (anydust) scoef = scoef + 2.0 * RK(h2dust) * HI * th.rhoH;
+    acoef = (RK(k13) * HI + RK(k11) * HII + RK(k12) * de) + RS(k29s) + RS(k31s);
+    if (anydust) scoef = scoef + 2.0 * RS(h2dust) * HI * th.rhoH;
     H2Ip = (scoef * dt + H2I) / (1.0 + acoef * dt);
 
     scoef = RK(k7) * HI * de;
@@ -350,18 +306,18 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
     HMp = (scoef * dt + HM) / (1.0 + acoef * dt);
 
     // H2+ at equilibrium with the NEW abundances (:2293-2301)
-    H2IIp = 2.0 * (RK(k9) * HIp * HIIp + RK(k11) * H2Ip / 2.0 * HIIp + RK(k17) * HMp * HIIp + RK(k29s) * H2Ip) /
-            (RK(k10) * HIp + RK(k18) * dep + RK(k19) * HMp + (RK(k28s) + RK(k30s)));
+    H2IIp = 2.0 * (RK(k9) * HIp * HIIp + RK(k11) * H2Ip / 2.0 * HIIp + RK(k17) * HMp * HIIp + RS(k29s) * H2Ip) /
+            (RK(k10) * HIp + RK(k18) * dep + RK(k19) * HMp + (RS(k28s) + RS(k30s)));
   }
 
   if (PC > 2) {
     const double HM = c.HM, H2I = c.H2I, DI = c.DI, DII = c.DII, HDI = c.HDI;
     scoef = (RK(k2) * DII * de + RK(k51) * DII * HI + 2.0 * RK(k55) * HDI * HI / 3.0);
-    acoef = RK(k1) * de + RK(k50) * HII + RK(k54) * H2I / 2.0 + RK(k56) * HM + RK(k24s);
+    acoef = RK(k1) * de + RK(k50) * HII + RK(k54) * H2I / 2.0 + RK(k56) * HM + RS(k24s);
     if (rt) acoef = acoef + kphHI;
     DIp = (scoef * dt + DI) / (1.0 + acoef * dt);
 
-    scoef = (RK(k1) * DI * de + RK(k50) * HII * DI + 2.0 * RK(k53) * HII * HDI / 3.0) + RK(k24s) * DI;
+    scoef = (RK(k1) * DI * de + RK(k50) * HII * DI + 2.0 * RK(k53) * HII * HDI / 3.0) + RS(k24s) * DI;
     if (rt) scoef = scoef + kphHI * DI;
     acoef = RK(k2) * de + RK(k51) * HI + RK(k52) * H2I / 2.0;
     DIIp = (scoef * dt + DII) / (1.0 + acoef * dt);
