@@ -175,6 +175,8 @@ def load_product():
     lib.grb200_kernel_launch_count.restype = C.c_longlong
     lib.grb200_device_available.restype = C.c_int
     lib.grb200_measure_fp64_tflops.restype = C.c_double
+    lib.grb200_set_solve_variant.argtypes = [C.c_int]
+    lib.grb200_set_solve_variant.restype = None
     return lib
 
 

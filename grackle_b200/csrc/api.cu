@@ -852,4 +852,6 @@ double grb200_measure_fp64_tflops(void)
 
 int grb200_device_available(void) { return device_ok() ? 1 : 0; }
 
+void grb200_set_solve_variant(int variant) { grb_solve_variant = variant; }
+
 }  // extern "C"

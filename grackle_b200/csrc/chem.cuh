@@ -108,7 +108,7 @@ __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool firs
         if (x > 10.0) {
           gamma2 = 0.5 * 5.0;
         } else {
-          const double ex = exp(x);
+          const double ex = dexp(x);
           gamma2 = 0.5 * (5.0 + 2.0 * (x * x) * ex / ((ex - 1) * (ex - 1)));
         }
       } else {
@@ -123,9 +123,9 @@ __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool firs
   if (first) tgasold = th.tgas;
 
   // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211)
-  th.logtgas = (PC > 0 && lookup_follows) ? log(th.tgas) : 0.0;
+  th.logtgas = (PC > 0 && lookup_follows) ? dlog(th.tgas) : 0.0;
 
-  double logtem = log(0.5 * (th.tgas + tgasold));
+  double logtem = dlog(0.5 * (th.tgas + tgasold));
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
   return logtem;
@@ -182,10 +182,10 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
       const double cieco = cv(L_CIECO);
       double tau = pow_pos((c.d / 2e16) * dom, 2.8);
       tau = dmax(tau, 1.e-5);
-      double ciefudge = dmin((1.0 - exp(-tau)) / tau, 1.0);
+      double ciefudge = dmin((1.0 - dexp(-tau)) / tau, 1.0);
       tau = pow_pos((c.d / 2.e18) * dom, 8.0);
       tau = dmax(tau, 1.e-5);
-      ciefudge = ciefudge * dmin((1.0 - exp(-tau)) / tau, 1.0);
+      ciefudge = ciefudge * dmin((1.0 - dexp(-tau)) / tau, 1.0);
       edot = ciefudge * (edot - c.H2I * (c.d * cieco));
     }
   }

@@ -64,10 +64,10 @@ __device__ inline double k13_martin(const GrParams &P, const Cell &c, const Ther
 #define DD(n) (slots[dd_slot(n)])
     double cid = DD(0) - DD(1) / (1.0 + pow_pos(nh / DD(4), DD(6))) + DD(2) -
                  DD(3) / (1.0 + pow_pos(nh / DD(5), DD(6)));
-    cid = dmax(exp10(cid), GRB_TINY8);
+    cid = dmax(dexp10(cid), GRB_TINY8);
     double dtn = DD(7) - DD(8) / (1.0 + pow_pos(nh / DD(11), DD(13))) + DD(9) -
                  DD(10) / (1.0 + pow_pos(nh / DD(12), DD(13)));
-    dtn = dmax(exp10(dtn), GRB_TINY8);
+    dtn = dmax(dexp10(dtn), GRB_TINY8);
     k13 = dtn + cid;
 #undef DD
   }
@@ -90,7 +90,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
     if (th.tdust > P.dtemend) {
       RS(h2dust) = GRB_TINY8;
     } else {
-      double dl = log(th.tdust);
+      double dl = dlog(th.tdust);
       dl = dmax(dl, P.d_logtem0);
       dl = dmin(dl, P.d_logtem9);
       const long long di = imin(P.ndratec - 1, imax(1, (long long)((dl - P.d_logtem0) / P.d_dlogtem) + 1));
@@ -133,12 +133,12 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
       tuse = dmin(tuse, 8e3);
       double nuse = c.d * dom / th.mmw;
       nuse = dmin(nuse, 1e7);
-      const double aWG = (0.8711 * log10(tuse) - 1.928) * exp(-0.2856 * log10(nuse)) +
-                         (-0.9639 * log10(tuse) + 3.892);
+      const double aWG = (0.8711 * dlog10(tuse) - 1.928) * dexp(-0.2856 * dlog10(nuse)) +
+                         (-0.9639 * dlog10(tuse) + 3.892);
       const double x = 2.0e-15 * N_H2;
       const double b_doppler = 1e-5 * sqrt(2.0 * GRB_KBOLTZ * th.tgas / GRB_MASS_H);
       double f_shield = 0.965 / pow_pos(1.0 + x / b_doppler, aWG) +
-                        0.035 * exp(-8.5e-4 * sqrt(1.0 + x)) / sqrt(1.0 + x);
+                        0.035 * dexp(-8.5e-4 * sqrt(1.0 + x)) / sqrt(1.0 + x);
       f_shield = dmin(f_shield, 1.0);
       RS(k31s) = f_shield * RS(k31s);
     }

@@ -8,6 +8,7 @@
 #define GRB200_PHYSICS_CUH
 
 #include "gr_device.h"
+#include "fastmath.cuh"
 
 namespace grb {
 
@@ -31,7 +32,7 @@ __device__ __forceinline__ double sq(double x) { return x * x; }
 // x**y for x >= 0 as exp(y ln x): every real power on this path has a non-negative base.
 // |y ln x| < 1e2 here, so the result is within ~1e-14 relative of the correctly rounded
 // power (the tolerances are 1e-9 / 1e-6) at well under half the instructions of pow().
-__device__ __forceinline__ double pow_pos(double x, double y) { return exp(y * log(x)); }
+__device__ __forceinline__ double pow_pos(double x, double y) { return dexp(y * dlog(x)); }
 __device__ __forceinline__ double pow4(double x) { const double x2 = x * x; return x2 * x2; }
 
 // 1-based clamped index on a uniform axis (interpolators_g.F:28-29 and friends)
@@ -108,12 +109,12 @@ __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, do
 {
   const double log10_tCMB = P.log10_tcmb;
   const double log10tem = logtem * GRB_INV_LN10;
-  const double log_n_h = log10(rhoH * P.dom);
-  double edot_met = -exp10(cloudy_lookup(c, c.cooling, log_n_h, log10tem));
+  const double log_n_h = dlog10(rhoH * P.dom);
+  double edot_met = -dexp10(cloudy_lookup(c, c.cooling, log_n_h, log10tem));
   if (icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
-    edot_met = edot_met + exp10(cloudy_lookup(c, c.cooling, log_n_h, log10_tCMB));
+    edot_met = edot_met + dexp10(cloudy_lookup(c, c.cooling, log_n_h, log10_tCMB));
   if (c.get_heat == 1)
-    edot_met = edot_met + exp10(cloudy_lookup(c, c.heating, log_n_h, log10tem));
+    edot_met = edot_met + dexp10(cloudy_lookup(c, c.heating, log_n_h, log10tem));
   if (iZscale == 1) edot_met = edot_met * metallicity;
   return edot_met * rhoH * rhoH;
 }
@@ -126,17 +127,17 @@ __device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c
   const double log10_tCMB = P.log10_tcmb;        // see oracle note on the unassigned upstream local
   const double log10tem = logtem * GRB_INV_LN10;
   double log_n_h = 0.0, log_Z = 0.0;
-  if (c.rank > 1) log_n_h = log10(rhoH * P.dom);
-  if (c.rank > 2) log_Z = log10(metallicity);
+  if (c.rank > 1) log_n_h = dlog10(rhoH * P.dom);
+  if (c.rank > 2) log_Z = dlog10(metallicity);
   auto look = [&](const double *data, double lt) {
     if (c.rank == 1) return interp1(c, data, lt);
     if (c.rank == 2) return interp2(c, data, log_n_h, lt);
     return interp3(c, data, log_n_h, log_Z, lt);
   };
-  double edot_met = -exp10(look(c.cooling, log10tem));
+  double edot_met = -dexp10(look(c.cooling, log10tem));
   if (P.icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
-    edot_met = edot_met + exp10(look(c.cooling, log10_tCMB));
-  if (P.iClHeat == 1) edot_met = edot_met + exp10(look(c.heating, log10tem));
+    edot_met = edot_met + dexp10(look(c.cooling, log10_tCMB));
+  if (P.iClHeat == 1) edot_met = edot_met + dexp10(look(c.heating, log10tem));
   return edot_met * rhoH * d;
 }
 
@@ -146,12 +147,12 @@ __device__ inline void temperature_table(const GrParams &P, double d, double e, 
 {
   const GrCloudyDev &c = P.pri;
   const double inv_log10 = GRB_INV_LN10;
-  const double log_n_h = log10(rhoH * P.dom);
+  const double log_n_h = dlog10(rhoH * P.dom);
   double munew = 1.0, muold = 1.0;
   for (int ti = 1; ti <= 20; ti++) {
     muold = munew;
     tgas = dmax((P.gamma - 1.0) * e * munew * P.utem, P.temstart);
-    const double log10tem = log(tgas) * inv_log10;
+    const double log10tem = dlog(tgas) * inv_log10;
     munew = cloudy_lookup(c, c.mmw, log_n_h, log10tem);
     munew = 0.5 * (munew + muold);
     tgas = tgas * munew / muold;

@@ -128,6 +128,11 @@ double grb200_measure_fp64_tflops(void);
 /* 1 if a CUDA device is usable, else 0 (never falls back to the CPU) */
 int grb200_device_available(void);
 
+/* solve-kernel instantiation: 0 (default) = pick per call (the compact instantiation when
+ * every optional physics module it omits is switched off, else the general one);
+ * 1 = always the general one.  Both give the same results; tests use 1 to prove it. */
+void grb200_set_solve_variant(int variant);
+
 #ifdef __cplusplus
 }
 #endif
