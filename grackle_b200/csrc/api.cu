@@ -51,6 +51,11 @@ struct DeviceCtx {
     double *slice_host = nullptr;          // pinned staging, 3 planes
     double slice_zr = 0.0;
     bool slice_valid = false;
+    // solve-kernel view of a rank-2 (n_H, T) table: [n_H][T] pairs (cooling, heating) followed
+    // by the cooling at T_CMB per n_H row; rebuilt when the redshift (hence T_CMB) changes
+    double *fast = nullptr, *fast_host = nullptr;
+    double fast_zr = 0.0;
+    bool fast_valid = false;
   } pri, met;
   // per-call scratch
   unsigned long long *diag = nullptr;      // 4 diagnostics + 1 work counter
@@ -175,6 +180,8 @@ void free_cloudy(DeviceCtx::Cloudy &c)
   cudaFree(c.cooling); cudaFree(c.heating); cudaFree(c.mmw);
   for (auto &p : c.slice) cudaFree(p);
   if (c.slice_host) cudaFreeHost(c.slice_host);
+  if (c.fast) cudaFree(c.fast);
+  if (c.fast_host) cudaFreeHost(c.fast_host);
 }
 
 }  // namespace
@@ -233,8 +240,12 @@ inline double pow5(double x) { const double x2 = x * x; return (x2 * x) * x2; }
 //     plane = v(z0) + log((1+zr)/(1+z0)) * (v(z1) - v(z0)) / log((1+z1)/(1+z0)).
 // The kernels then do a rank-2 lookup: 4 gathers and no logarithm per interpolation
 // instead of 8 gathers and 2 logarithms.
+int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, const double *heat,
+                      const double *par_n, const double *par_t, long long n0, long long nt, double zr,
+                      double log10_tcmb, cudaStream_t st);
+
 int cloudy_params(GrCloudyDev &d, DeviceCtx::Cloudy &c, const cloudy_data &h, double zr, int iClHeat,
-                  int clnew, cudaStream_t st)
+                  int clnew, double log10_tcmb, cudaStream_t st)
 {
   std::memset(&d, 0, sizeof(d));
   d.rank = c.rank;
@@ -248,6 +259,9 @@ int cloudy_params(GrCloudyDev &d, DeviceCtx::Cloudy &c, const cloudy_data &h, do
     const long long n = h.grid_dimension[q];
     d.dpar[q] = (p[n - 1] - p[0]) / (double)(n - 1);
   }
+  if (c.rank == 2 && clnew == 1 && h.cooling_data)
+    return cloudy_fast_plane(d, c, h.cooling_data, (iClHeat == 1) ? h.heating_data : nullptr, h.grid_parameters[0],
+                             h.grid_parameters[1], h.grid_dimension[0], h.grid_dimension[1], zr, log10_tcmb, st);
   if (c.rank != 3 || clnew != 1) return GR_SUCCESS;
 
   // redshift index by bisection, 1-based (cool1d_cloudy_g.F:128-153)
@@ -314,6 +328,55 @@ int cloudy_params(GrCloudyDev &d, DeviceCtx::Cloudy &c, const cloudy_data &h, do
   d.heating = h.heating_data ? c.slice[1] : nullptr;
   d.mmw = h.mmw_data ? c.slice[2] : nullptr;
   d.zindex = zindex; d.end_int = end_int;
+  if (h.cooling_data)
+    return cloudy_fast_plane(d, c, c.slice_host, (h.heating_data && d.get_heat == 1) ? c.slice_host + plane : nullptr,
+                             h.grid_parameters[0], h.grid_parameters[2], n0, nt, zr, log10_tcmb, st);
+  return GR_SUCCESS;
+}
+
+// The solve kernel's view of a rank-2 (n_H, T) table (physics.cuh cloudy_edot_fast): cooling
+// and heating interleaved so that one 16-byte gather serves both, uniform-axis origin and
+// inverse spacing instead of axis gathers and divisions, and the CMB-floor term - cooling at
+// T_CMB, the same for every cell of a call - interpolated along T here, once per row, with the
+// reference's own formula (interpolators_g.F:45-101) so the kernel only interpolates along n_H.
+int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, const double *heat,
+                      const double *par_n, const double *par_t, long long n0, long long nt, double zr,
+                      double log10_tcmb, cudaStream_t st)
+{
+  const size_t plane = (size_t)n0 * (size_t)nt;
+  const size_t elems = 2 * plane + (size_t)n0;
+  if (!c.fast_host) {
+    CUDA_OK(cudaMallocHost(&c.fast_host, elems * sizeof(double)));
+    CUDA_OK(cudaMalloc(&c.fast, elems * sizeof(double)));
+  }
+  if (!c.fast_valid || c.fast_zr != zr) {
+    CUDA_OK(cudaStreamSynchronize(st));
+    for (size_t q = 0; q < plane; q++) {
+      c.fast_host[2 * q] = cool[q];
+      c.fast_host[2 * q + 1] = heat ? heat[q] : 0.0;
+    }
+    const double dpar_t = (par_t[nt - 1] - par_t[0]) / (double)(nt - 1);
+    long long i2 = (long long)((log10_tcmb - par_t[0]) / dpar_t) + 1;
+    i2 = std::min(nt - 1, std::max(1LL, i2));
+    for (long long i = 0; i < n0; i++) {
+      const double *row = cool + (size_t)i * nt;
+      const double slope = (row[i2] - row[i2 - 1]) / (par_t[i2] - par_t[i2 - 1]);
+      c.fast_host[2 * plane + i] = (log10_tcmb - par_t[i2 - 1]) * slope + row[i2 - 1];
+    }
+    CUDA_OK(cudaMemcpyAsync(c.fast, c.fast_host, elems * sizeof(double), cudaMemcpyHostToDevice, st));
+    c.fast_zr = zr;
+    c.fast_valid = true;
+  }
+  d.fast = 1;
+  d.ch = c.fast;
+  d.cmb = c.fast + 2 * plane;
+  d.heat_in_ch = heat ? 1 : 0;
+  d.par0[0] = par_n[0]; d.par0[1] = par_t[0];
+  d.inv_dpar[0] = 1.0 / ((par_n[n0 - 1] - par_n[0]) / (double)(n0 - 1));
+  d.inv_dpar[1] = 1.0 / ((par_t[nt - 1] - par_t[0]) / (double)(nt - 1));
+  d.fdpar[0] = (par_n[n0 - 1] - par_n[0]) / (double)(n0 - 1);
+  d.fdpar[1] = (par_t[nt - 1] - par_t[0]) / (double)(nt - 1);
+  d.fdim[0] = (int)n0; d.fdim[1] = (int)nt;
   return GR_SUCCESS;
 }
 
@@ -392,15 +455,18 @@ int fill_params(GrParams &P, DeviceCtx *ctx, const chemistry_data *chem,
   P.d_logtem0 = std::log(P.dtemstart); P.d_logtem9 = std::log(P.dtemend);
   P.d_dlogtem = (std::log(P.dtemend) - std::log(P.dtemstart)) / (double)(P.ndratec - 1);
   P.a3 = cube(P.aye); P.a3inv = 1.0 / cube(P.aye);
+  P.inv_dlogtem = 1.0 / P.dlogtem; P.inv_gm1 = 1.0 / (P.gamma - 1.0); P.inv_zsolar = 1.0 / P.z_solar;
   P.ssh_sig_hi = 6.73e-3 * std::pow(P.avgsighi / 2.49e-18, -2.0 / 3.0);
   P.ssh_sig_hei = 6.73e-3 * std::pow(P.avgsighei / 2.49e-18, -2.0 / 3.0);
   P.ssh_k24 = std::pow(P.k24 / P.tbase1 / 1.0e-12, 2.0 / 3.0);
   P.ssh_k26 = std::pow(P.k26 / P.tbase1 / 1.0e-12, 2.0 / 3.0);
 
   P.chem = ctx->chem; P.cool = ctx->cool; P.h2dust = ctx->h2dust; P.k13a = ctx->k13a; P.k22a = ctx->k22a;
-  if (cloudy_params(P.pri, ctx->pri, rates->cloudy_primordial, P.zr, P.iClHeat, P.clnew, ctx->stream()) == GR_FAIL)
+  if (cloudy_params(P.pri, ctx->pri, rates->cloudy_primordial, P.zr, P.iClHeat, P.clnew, P.log10_tcmb,
+                    ctx->stream()) == GR_FAIL)
     return GR_FAIL;
-  if (cloudy_params(P.met, ctx->met, rates->cloudy_metal, P.zr, P.iClHeat, P.clnew, ctx->stream()) == GR_FAIL)
+  if (cloudy_params(P.met, ctx->met, rates->cloudy_metal, P.zr, P.iClHeat, P.clnew, P.log10_tcmb,
+                    ctx->stream()) == GR_FAIL)
     return GR_FAIL;
   P.diag = ctx->diag;
   P.work_counter = ctx->diag + 4;

@@ -60,10 +60,12 @@ struct TIndex { int idx; double t1, t2, tdef; };   // idx is 1-based like the Fo
 __device__ __forceinline__ TIndex t_index(const GrParams &P, double logtem)
 {
   TIndex r;
-  r.idx = (int)imin(P.nratec - 1, imax(1, (long long)((logtem - P.logtem0) / P.dlogtem) + 1));
+  // (x - x0) / dlogtem and (x - t1) / (t2 - t1) as multiplications by 1/dlogtem: t2 - t1 is
+  // dlogtem to within one rounding, and the interpolant is continuous across a bin edge
+  r.idx = min(P.nratec - 1, max(1, (int)((logtem - P.logtem0) * P.inv_dlogtem) + 1));
   r.t1 = (P.logtem0 + (r.idx - 1) * P.dlogtem);
   r.t2 = (P.logtem0 + (r.idx) * P.dlogtem);
-  r.tdef = (logtem - r.t1) / (r.t2 - r.t1);
+  r.tdef = (logtem - r.t1) * P.inv_dlogtem;
   return r;
 }
 
@@ -97,29 +99,30 @@ __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool firs
       th.rhoH = th.rhoH + c.H2I + c.H2II;
     }
     if (P.imetal == 1) mmw = mmw + c.metal / GRB_MU_METAL;
-    th.tgas = dmax(th.p2d * P.utem / mmw, P.temstart);
-    th.mmw = c.d / mmw;
+    const double rmmw = drcp(mmw);
+    th.tgas = dmax(th.p2d * P.utem * rmmw, P.temstart);
+    th.mmw = c.d * rmmw;
     if (PC > 1) {    // H2 vibrational gamma correction (:294-318)
       const double nH2 = 0.5 * (c.H2I + c.H2II);
       const double nother = (c.HeI + c.HeII + c.HeIII) / 4.0 + c.HI + c.HII + c.de;
       double gamma2;
-      if (nH2 / nother > 1.0e-3) {
-        const double x = 6100.0 / th.tgas;
+      if (nH2 > 1.0e-3 * nother) {
+        const double x = ddiv(6100.0, th.tgas);
         if (x > 10.0) {
           gamma2 = 0.5 * 5.0;
         } else {
           const double ex = dexp(x);
-          gamma2 = 0.5 * (5.0 + 2.0 * (x * x) * ex / ((ex - 1) * (ex - 1)));
+          gamma2 = 0.5 * (5.0 + ddiv(2.0 * (x * x) * ex, (ex - 1) * (ex - 1)));
         }
       } else {
         gamma2 = 2.5;
       }
-      gamma2 = 1.0 + (nH2 + nother) / (nH2 * gamma2 + nother / (P.gamma - 1.0));
-      th.tgas = th.tgas * (gamma2 - 1.0) / (P.gamma - 1.0);
+      gamma2 = 1.0 + ddiv(nH2 + nother, nH2 * gamma2 + nother * P.inv_gm1);
+      th.tgas = th.tgas * (gamma2 - 1.0) * P.inv_gm1;
     }
   }
 
-  if (P.imetal == 1) th.metallicity = c.metal / c.d / P.z_solar;
+  if (P.imetal == 1) th.metallicity = ddiv(c.metal, c.d) * P.inv_zsolar;
   if (first) tgasold = th.tgas;
 
   // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211)
@@ -176,8 +179,8 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
       fudge = dmin(fudge, 1.0);
     }
     const double galdl = gaHI * c.HI + gaH2 * c.H2I / 2.0 + gaHe * c.HeI / 4.0 + gaHp * c.HII + gael * c.de;
-    const double gphdl1 = h2lte / dom;
-    edot = edot - (double)P.ih2co * fudge * c.H2I * h2lte / (1.0 + gphdl1 / galdl) / (2.0 * dom);
+    const double gphdl1 = h2lte * dom_inv;
+    edot = edot - ddiv((double)P.ih2co * fudge * c.H2I * h2lte, 1.0 + ddiv(gphdl1, galdl)) * (0.5 * dom_inv);
     if (P.iciecool == 1 && c.d * dom > 1e10) {
       const double cieco = cv(L_CIECO);
       double tau = pow_pos((c.d / 2e16) * dom, 2.8);
@@ -194,9 +197,9 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     double hdlte, hdlow;
     if (th.tgas > P.comp2) { hdlte = cv(L_HDLTE); hdlow = cv(L_HDLOW); }
     else { hdlte = GRB_TINY; hdlow = GRB_TINY; }
-    const double hdlte1 = hdlte / (c.HI * dom);
+    const double hdlte1 = ddiv(hdlte, c.HI * dom);
     const double hdlow1 = dmax(hdlow, GRB_TINY);
-    edot = edot - c.HDI * (hdlte / (1.0 + hdlte1 / hdlow1)) / (3.0 * dom);
+    edot = edot - c.HDI * ddiv(hdlte, 1.0 + ddiv(hdlte1, hdlow1)) * ((1.0 / 3.0) * dom_inv);
   }
 
   if (anydust || (P.igammah > 0))
@@ -223,7 +226,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     }
     const double ip = (double)P.ipiht;
     if (P.iradshield == 0)
-      edot = edot + ip * (P.piHI * c.HI + P.piHeI * c.HeI * 0.25 + P.piHeII * c.HeII * 0.25) / dom;
+      edot = edot + ip * (P.piHI * c.HI + P.piHeI * c.HeI * 0.25 + P.piHeII * c.HeII * 0.25) * dom_inv;
     else if (P.iradshield == 1)
       edot = edot + ip * (P.piHI * c.HI * fH + P.piHeI * c.HeI * 0.25 + P.piHeII * c.HeII * 0.25) / dom;
     else if (P.iradshield == 2)

@@ -58,6 +58,13 @@ struct GrCloudyDev {
   long long zindex;        // 1-based index into the redshift axis
   int end_int;             // redshift beyond the table: use the last z-plane (2Df3D)
   int get_heat;            // heating table applies at this redshift
+  // solve-kernel view of a new-style rank-2 (n_H, T) table (api.cu cloudy_fast_plane)
+  int fast;                // 1 when the fields below are set
+  int heat_in_ch;          // the pairs carry a heating value
+  int fdim[2];             // n_H, T points
+  const double *ch;        // [n_H][T][2] = (cooling, heating)
+  const double *cmb;       // [n_H] cooling at T_CMB
+  double par0[2], inv_dpar[2], fdpar[2];   // axis origin, 1/spacing, spacing
 };
 
 // the 15 density-like fields + energy, in the order the kernels index them
@@ -93,6 +100,7 @@ struct GrParams {
   double log10_tcmb;                 // log10(comp2), cell-invariant (cool1d_cloudy_g.F:110)
   double zr, comp1, comp2, logtem0, logtem9, dlogtem, d_logtem0, d_logtem9, d_dlogtem;
   double a3, a3inv;                  // comoving <-> proper factors (aye^3, aye^-3)
+  double inv_dlogtem, inv_gm1, inv_zsolar;   // 1/dlogtem, 1/(gamma-1), 1/z_solar (divisions by cell-invariants -> multiplications)
   // Rahmati+13 cell-invariant factors: 6.73e-3*(sig/2.49e-18)^(-2/3) and (k/tbase1/1e-12)^(2/3)
   double ssh_sig_hi, ssh_sig_hei, ssh_k24, ssh_k26;
   // tables

@@ -547,6 +547,7 @@ __host__ __device__ inline void lean_flags(GrParams &P)
   P.idust = 0; P.idustall = 0; P.idustfield = 0; P.idustrec = 0; P.igammah = 0; P.ih2optical = 0;
   P.iciecool = 0; P.ithreebody = 0; P.iH2shield = 0; P.iradshield = 0; P.iradtrans = 0; P.iradcoupled = 0;
   P.iVheat = 0; P.iMheat = 0; P.iisrffield = 0; P.iH2shieldcustom = 0; P.clnew = 1;
+  P.met.fast = 1; P.pri.fast = 1;
 }
 
 template <int PC, bool LEAN>
@@ -644,7 +645,8 @@ bool grb_solve_is_lean(const GrParams &P)
   const bool off = P.idust <= 0 && P.idustall <= 0 && P.idustfield <= 0 && P.idustrec <= 0 && P.igammah <= 0 &&
                    P.ih2optical <= 0 && P.iciecool <= 0 && P.iH2shield <= 0 && P.iradshield <= 0 &&
                    P.iradtrans <= 0 && P.iVheat <= 0 && P.iMheat <= 0 && P.iisrffield <= 0 && P.iH2shieldcustom <= 0;
-  return off && (P.ispecies < 2 || P.ithreebody == 0) && (P.imcool == 0 || P.clnew == 1);
+  return off && (P.ispecies < 2 || P.ithreebody == 0) && (P.imcool == 0 || (P.clnew == 1 && P.met.fast == 1)) &&
+         (P.ispecies > 0 || P.pri.fast == 1);
 }
 
 // persistent launch: `blocks` CTAs of GRB_SOLVE_THREADS threads (host picks a multiple of

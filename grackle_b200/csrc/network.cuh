@@ -62,11 +62,11 @@ __device__ inline double k13_martin(const GrParams &P, const Cell &c, const Ther
   double k13 = GRB_TINY8;
   if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
 #define DD(n) (slots[dd_slot(n)])
-    double cid = DD(0) - DD(1) / (1.0 + pow_pos(nh / DD(4), DD(6))) + DD(2) -
-                 DD(3) / (1.0 + pow_pos(nh / DD(5), DD(6)));
+    double cid = DD(0) - ddiv(DD(1), 1.0 + pow_pos(ddiv(nh, DD(4)), DD(6))) + DD(2) -
+                 ddiv(DD(3), 1.0 + pow_pos(ddiv(nh, DD(5)), DD(6)));
     cid = dmax(dexp10(cid), GRB_TINY8);
-    double dtn = DD(7) - DD(8) / (1.0 + pow_pos(nh / DD(11), DD(13))) + DD(9) -
-                 DD(10) / (1.0 + pow_pos(nh / DD(12), DD(13)));
+    double dtn = DD(7) - ddiv(DD(8), 1.0 + pow_pos(ddiv(nh, DD(11)), DD(13))) + DD(9) -
+                 ddiv(DD(10), 1.0 + pow_pos(ddiv(nh, DD(12)), DD(13)));
     dtn = dmax(dexp10(dtn), GRB_TINY8);
     k13 = dtn + cid;
 #undef DD
@@ -206,7 +206,7 @@ __device__ inline void rate_derivs(const GrParams &P, const Cell &c, const Therm
             + (RS(k24s) * HI + RS(k25s) * HeII / 4.0 + RS(k26s) * HeI / 4.0);
 
     // H2 formation heating, Omukai (2000) eq. 23
-    const double h2heatfac = 1.0 / (1.0 + (RK(ncrn) / (P.dom * (HI * RK(ncrd1) + H2I * 0.5 * RK(ncrd2)))));
+    const double h2heatfac = drcp(1.0 + ddiv(RK(ncrn), P.dom * (HI * RK(ncrd1) + H2I * 0.5 * RK(ncrd2))));
     double H2delta = HI * (4.48 * RK(k22) * (HI * HI) - 4.48 * RK(k13) * H2I / 2.0);
     if (H2delta > 0.0) H2delta = H2delta * h2heatfac;
     if (anydust) H2delta = H2delta + RS(h2dust) * HI * th.rhoH * (0.2 + 4.2 * h2heatfac);
@@ -243,12 +243,12 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
     scoef = RK(k2) * HII * de;
     acoef = RK(k1) * de + RK(k57) * HI + RK(k58) * HeI / 4.0 + RS(k24s);
     if (rt) acoef = acoef + kphHI;
-    HIp = (scoef * dt + HI) / (1.0 + acoef * dt);
+    HIp = ddiv((scoef * dt + HI), (1.0 + acoef * dt));
 
     scoef = RK(k1) * HIp * de + RK(k57) * HIp * HIp + RK(k58) * HIp * HeI / 4.0 + RS(k24s) * HIp;
     if (rt) scoef = scoef + kphHI * HIp;
     acoef = RK(k2) * de;
-    HIIp = (scoef * dt + HII) / (1.0 + acoef * dt);
+    HIIp = ddiv((scoef * dt + HII), (1.0 + acoef * dt));
     // (the reference also forms dep here and then discards it)
   }
 
@@ -256,18 +256,18 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
   scoef = RK(k4) * HeII * de;
   acoef = RK(k3) * de + RS(k26s);
   if (rt_all) acoef = acoef + kphHeI;
-  const double HeIp = (scoef * dt + HeI) / (1.0 + acoef * dt);
+  const double HeIp = ddiv((scoef * dt + HeI), (1.0 + acoef * dt));
 
   scoef = RK(k3) * HeIp * de + RK(k6) * HeIII * de + RS(k26s) * HeIp;
   if (rt_all) scoef = scoef + kphHeI * HeIp;
   acoef = RK(k4) * de + RK(k5) * de + RS(k25s);
   if (rt_all) acoef = acoef + kphHeII;
-  const double HeIIp = (scoef * dt + HeII) / (1.0 + acoef * dt);
+  const double HeIIp = ddiv((scoef * dt + HeII), (1.0 + acoef * dt));
 
   scoef = RK(k5) * HeIIp * de + RS(k25s) * HeIIp;
   if (rt_all) scoef = scoef + kphHeII * HeIIp;
   acoef = RK(k6) * de;
-  const double HeIIIp = (scoef * dt + HeIII) / (1.0 + acoef * dt);
+  const double HeIIIp = ddiv((scoef * dt + HeIII), (1.0 + acoef * dt));
 
   if (PC > 1) {
     const double HM = c.HM, H2I = c.H2I, H2II = c.H2II;
@@ -279,13 +279,13 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
             2.0 * RK(k22) * (HI * HI) + RK(k57) * HI + RK(k58) * HeI / 4.0 + RS(k24s);
     if (rt) acoef = acoef + kphHI;
     if (anydust) acoef = acoef + 2.0 * RS(h2dust) * th.rhoH;
-    HIp = (scoef * dt + HI) / (1. + acoef * dt);
+    HIp = ddiv((scoef * dt + HI), (1. + acoef * dt));
 
     scoef = RK(k1) * HI * de + RK(k10) * H2II * HI / 2.0 + RK(k57) * HI * HI + RK(k58) * HI * HeI / 4.0 +
             RS(k24s) * HI;
     if (rt) scoef = scoef + kphHI * HI;
     acoef = RK(k2) * de + RK(k9) * HI + RK(k11) * H2I / 2.0 + RK(k16) * HM + RK(k17) * HM;
-    HIIp = (scoef * dt + HII) / (1.0 + acoef * dt);
+    HIIp = ddiv((scoef * dt + HII), (1.0 + acoef * dt));
 
     scoef = RK(k8) * HM * HI + RK(k15) * HM * HI + RK(k17) * HM * HII + RK(k57) * HI * HI +
             RK(k58) * HI * HeI / 4.0 + RS(k24s) * HIp + RS(k25s) * HeIIp / 4.0 + RS(k26s) * HeIp / 4.0;
@@ -299,37 +299,38 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
                    RK(k22) * HI * (HI * HI));
     acoef = (RK(k13) * HI + RK(k11) * HII + RK(k12) * de) + RS(k29s) + RS(k31s);
     if (anydust) scoef = scoef + 2.0 * RS(h2dust) * HI * th.rhoH;
-    H2Ip = (scoef * dt + H2I) / (1.0 + acoef * dt);
+    H2Ip = ddiv((scoef * dt + H2I), (1.0 + acoef * dt));
 
     scoef = RK(k7) * HI * de;
     acoef = (RK(k8) + RK(k15)) * HI + (RK(k16) + RK(k17)) * HII + RK(k14) * de + RK(k19) * H2II / 2.0 + P.k27;
-    HMp = (scoef * dt + HM) / (1.0 + acoef * dt);
+    HMp = ddiv((scoef * dt + HM), (1.0 + acoef * dt));
 
     // H2+ at equilibrium with the NEW abundances (:2293-2301)
-    H2IIp = 2.0 * (RK(k9) * HIp * HIIp + RK(k11) * H2Ip / 2.0 * HIIp + RK(k17) * HMp * HIIp + RS(k29s) * H2Ip) /
-            (RK(k10) * HIp + RK(k18) * dep + RK(k19) * HMp + (RS(k28s) + RS(k30s)));
+    H2IIp = ddiv(2.0 * (RK(k9) * HIp * HIIp + RK(k11) * H2Ip / 2.0 * HIIp + RK(k17) * HMp * HIIp + RS(k29s) * H2Ip),
+                 RK(k10) * HIp + RK(k18) * dep + RK(k19) * HMp + (RS(k28s) + RS(k30s)));
   }
 
   if (PC > 2) {
     const double HM = c.HM, H2I = c.H2I, DI = c.DI, DII = c.DII, HDI = c.HDI;
-    scoef = (RK(k2) * DII * de + RK(k51) * DII * HI + 2.0 * RK(k55) * HDI * HI / 3.0);
+    scoef = (RK(k2) * DII * de + RK(k51) * DII * HI + 2.0 * RK(k55) * HDI * HI * (1.0 / 3.0));
     acoef = RK(k1) * de + RK(k50) * HII + RK(k54) * H2I / 2.0 + RK(k56) * HM + RS(k24s);
     if (rt) acoef = acoef + kphHI;
-    DIp = (scoef * dt + DI) / (1.0 + acoef * dt);
+    DIp = ddiv((scoef * dt + DI), (1.0 + acoef * dt));
 
-    scoef = (RK(k1) * DI * de + RK(k50) * HII * DI + 2.0 * RK(k53) * HII * HDI / 3.0) + RS(k24s) * DI;
+    scoef = (RK(k1) * DI * de + RK(k50) * HII * DI + 2.0 * RK(k53) * HII * HDI * (1.0 / 3.0)) + RS(k24s) * DI;
     if (rt) scoef = scoef + kphHI * DI;
     acoef = RK(k2) * de + RK(k51) * HI + RK(k52) * H2I / 2.0;
-    DIIp = (scoef * dt + DII) / (1.0 + acoef * dt);
+    DIIp = ddiv((scoef * dt + DII), (1.0 + acoef * dt));
 
     scoef = 3.0 * (RK(k52) * DII * H2I / 2.0 / 2.0 + RK(k54) * DI * H2I / 2.0 / 2.0 +
                    2.0 * RK(k56) * DI * HM / 2.0);
     acoef = RK(k53) * HII + RK(k55) * HI;
-    HDIp = (scoef * dt + HDI) / (1.0 + acoef * dt);
+    HDIp = ddiv((scoef * dt + HDI), (1.0 + acoef * dt));
   }
 
   // write back with floors (:2364-2397)
-  HIdot_prev = fabs(c.HI - HIp) / dmax(dt, GRB_TINY8);
+  const double rdt = drcp(dmax(dt, GRB_TINY8));
+  HIdot_prev = fabs(c.HI - HIp) * rdt;
   c.HI = dmax(HIp, GRB_TINY);
   c.HII = dmax(HIIp, GRB_TINY);
   c.HeI = dmax(HeIp, GRB_TINY);
@@ -338,7 +339,7 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
   const double de_old = c.de;
   c.de = c.HII + c.HeII / 4.0 + c.HeIII / 2.0;
   if (PC > 1) c.de = c.de - c.HM + c.H2II / 2.0;     // old HM, H2II
-  dedot_prev = fabs(c.de - de_old) / dmax(dt, GRB_TINY8);
+  dedot_prev = fabs(c.de - de_old) * rdt;
   if (PC > 1) {
     c.HM = dmax(HMp, GRB_TINY);
     c.H2I = dmax(H2Ip, GRB_TINY);

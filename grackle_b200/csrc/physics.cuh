@@ -104,9 +104,47 @@ __device__ inline double cloudy_lookup(const GrCloudyDev &c, const double *data,
 }
 
 // ---- cool1d_cloudy_g (cool1d_cloudy_g.F:4-261): returns the edot increment -------
+// Fast form for a rank-2 (n_H, T) table prepared by the host (api.cu cloudy_fast_plane): the
+// same bilinear interpolation as interpolate_2D_g (interpolators_g.F:45-101; index clamped,
+// weights not, so it extrapolates linearly like the reference), with
+//   * cooling and heating read as one (cooling, heating) pair per grid point: 4 gathers serve
+//     both lookups instead of 8 gathers + 8 axis gathers,
+//   * axis values formed from origin + i * spacing and divisions by the spacing replaced by
+//     multiplications with its inverse (the grids are uniform; the difference to the stored
+//     axis values is one rounding, ~1e-16),
+//   * the CMB-floor term (cooling at T_CMB, cell-invariant along T) read from a per-row array.
+__device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCloudyDev &c, double rhoH,
+                                                   double metallicity, double logtem, int icmbTfloor,
+                                                   int iZscale)
+{
+  const double log10tem = logtem * GRB_INV_LN10;
+  const double log_n_h = dlog10(rhoH * P.dom);
+  int i1 = (int)((log_n_h - c.par0[0]) * c.inv_dpar[0]) + 1;
+  i1 = min(c.fdim[0] - 1, max(1, i1));
+  int i2 = (int)((log10tem - c.par0[1]) * c.inv_dpar[1]) + 1;
+  i2 = min(c.fdim[1] - 1, max(1, i2));
+  const double w1 = (log_n_h - (c.par0[0] + (double)(i1 - 1) * c.fdpar[0])) * c.inv_dpar[0];
+  const double w2 = (log10tem - (c.par0[1] + (double)(i2 - 1) * c.fdpar[1])) * c.inv_dpar[1];
+  const double2 *g = reinterpret_cast<const double2 *>(c.ch) + ((i1 - 1) * c.fdim[1] + (i2 - 1));
+  const double2 v00 = __ldg(g), v01 = __ldg(g + 1), v10 = __ldg(g + c.fdim[1]), v11 = __ldg(g + c.fdim[1] + 1);
+  const bool floor_on = (icmbTfloor == 1) && ((log10tem - P.log10_tcmb) < 2.0);
+  double m0 = 0.0, m1 = 0.0;
+  if (floor_on) { m0 = ld(c.cmb + i1 - 1); m1 = ld(c.cmb + i1); }
+  const double c0 = w2 * (v01.x - v00.x) + v00.x, c1 = w2 * (v11.x - v10.x) + v10.x;
+  double edot_met = -dexp10(w1 * (c1 - c0) + c0);
+  if (floor_on) edot_met = edot_met + dexp10(w1 * (m1 - m0) + m0);
+  if (c.get_heat == 1) {
+    const double h0 = w2 * (v01.y - v00.y) + v00.y, h1 = w2 * (v11.y - v10.y) + v10.y;
+    edot_met = edot_met + dexp10(w1 * (h1 - h0) + h0);
+  }
+  if (iZscale == 1) edot_met = edot_met * metallicity;
+  return edot_met * rhoH * rhoH;
+}
+
 __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, double rhoH,
                                      double metallicity, double logtem, int icmbTfloor, int iZscale)
 {
+  if (c.fast == 1) return cloudy_edot_fast(P, c, rhoH, metallicity, logtem, icmbTfloor, iZscale);
   const double log10_tCMB = P.log10_tcmb;
   const double log10tem = logtem * GRB_INV_LN10;
   const double log_n_h = dlog10(rhoH * P.dom);

@@ -1,0 +1,23 @@
+"""grackle_b200/csrc/fastmath.cuh (the solve kernel's lean log / exp / exp10 / divide) compiled
+for the host and checked against libm in long double over the argument ranges of the path.
+The device build uses the same source with MUFU.RCP64H as the reciprocal seed."""
+import os
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_fastmath_matches_libm(tmp_path):
+    exe = str(tmp_path / "fastmath_host")
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-o", exe,
+                    os.path.join(ROOT, "tests", "fastmath_host.cpp")], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
+    rows = {ln.split()[0]: ln.split()[1:] for ln in out.strip().splitlines()}
+    assert rows["special"] == ["ok"], out          # NaN / Inf / 0 / negative / out-of-range -> libm result
+    # max error in ulp of the exact result
+    limits = {"log_wide": 3.0, "log_near1": 3.0, "log10": 4.0, "exp": 1.5, "exp_small": 1.5,
+              "exp10": 2.0, "exp10_small": 2.0, "rcp": 1.0, "div": 1.0}
+    for name, lim in limits.items():
+        assert float(rows[name][0]) <= lim, (name, rows[name])
+    # x**y = exp(y ln x) amplifies the log error by |y ln x| (here <= 38): relative bound instead
+    assert float(rows["pow"][1]) <= 2e-14, rows["pow"]
