@@ -180,7 +180,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     }
     const double galdl = gaHI * c.HI + gaH2 * c.H2I / 2.0 + gaHe * c.HeI / 4.0 + gaHp * c.HII + gael * c.de;
     const double gphdl1 = h2lte * dom_inv;
-    edot = edot - ddiv((double)P.ih2co * fudge * c.H2I * h2lte, 1.0 + ddiv(gphdl1, galdl)) * (0.5 * dom_inv);
+    edot = edot - ddiv_s((double)P.ih2co * fudge * c.H2I * h2lte, 1.0 + ddiv_s(gphdl1, galdl)) * (0.5 * dom_inv);
     if (P.iciecool == 1 && c.d * dom > 1e10) {
       const double cieco = cv(L_CIECO);
       double tau = pow_pos((c.d / 2e16) * dom, 2.8);

@@ -110,12 +110,29 @@ GRB_FM_HD double drcp(double b)
   return fma(r, e, r);
 }
 
-// a/b under the same conditions (one residual correction: within 1 ulp)
+// a/b under the same conditions (one residual correction: within 1 ulp).  NOT for
+// denominators that can be zero or non-finite: the result would be NaN, not Inf - use ddiv_s.
 GRB_FM_HD double ddiv(double a, double b)
 {
+#ifdef GRB_DDIV_IEEE
+  return a / b;
+#endif
   const double r = drcp(b);
   const double q = a * r;
   return fma(fma(-b, q, a), r, q);
+}
+
+// a/b for ANY b: zero, subnormal, Inf and NaN denominators take the IEEE division (a/0 = Inf is
+// meaningful on this path: a vanishing rate in a denominator must switch the term off)
+#ifdef __CUDACC__
+__device__ __noinline__ double fm_div_slow(double a, double b) { return a / b; }
+#else
+static inline double fm_div_slow(double a, double b) { return a / b; }
+#endif
+GRB_FM_HD double ddiv_s(double a, double b)
+{
+  if ((unsigned)((fm_hi(b) & 0x7ff00000) - 0x00100000) >= 0x7fe00000u) return fm_div_slow(a, b);
+  return ddiv(a, b);
 }
 
 // natural logarithm

@@ -20,23 +20,31 @@ namespace grb {
 __device__ __forceinline__ size_t cell_index(const GrParams &P, long long t, int &i, int &j, int &k)
 {
   const int ni = P.ie - P.is + 1, nj = P.je - P.js + 1;
-  i = (int)(t % ni) + P.is;
-  const long long r = t / ni;
-  j = (int)(r % nj) + P.js;
-  k = (int)(r / nj) + P.ks;
+  if (P.nactive <= 0x7fffffffLL) {      // 32-bit divisions (1024^3 = 2^30 cells still qualifies)
+    const unsigned tt = (unsigned)t, r = tt / (unsigned)ni;
+    i = (int)(tt - r * (unsigned)ni) + P.is;
+    const unsigned q = r / (unsigned)nj;
+    j = (int)(r - q * (unsigned)nj) + P.js;
+    k = (int)q + P.ks;
+  } else {
+    i = (int)(t % ni) + P.is;
+    const long long r = t / ni;
+    j = (int)(r % nj) + P.js;
+    k = (int)(r / nj) + P.ks;
+  }
   return (size_t)i + (size_t)P.in * ((size_t)j + (size_t)P.jn * (size_t)k);
 }
 
 // Load one cell, converting comoving -> proper in registers (scale_fields_g) and applying
 // the species floors (ceiling_species_g) when `floors` is set (solve only).
-template <int PC>
+template <int PC, bool SCALE_DIV>
 __device__ __forceinline__ void load_cell(const GrParams &P, size_t x, Cell &c, bool floors)
 {
   const double s = (P.iexpand == 1) ? P.a3inv : 1.0;
   const bool sc = (P.iexpand == 1);
   // solve multiplies by aye**(-3) (solve_rate_cool_g.F:353); cooling time divides by aye**3
   // (cool_multi_time_g.F:163): keep each spelling so roundings match
-#define LDF(id) (sc ? (P.scale_div ? P.f[id][x] / P.a3 : P.f[id][x] * s) : P.f[id][x])
+#define LDF(id) (sc ? (SCALE_DIV ? P.f[id][x] / P.a3 : P.f[id][x] * s) : P.f[id][x])
   c.d = LDF(F_D);
   c.e = P.f[F_E][x];
   c.metal = (P.imetal == 1) ? LDF(F_METAL) : 0.0;
@@ -176,7 +184,7 @@ __global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ Gr
   int i, j, k;
   const size_t x = cell_index(P, t, i, j, k);
   Cell c;
-  load_cell<PC>(P, x, c, false);
+  load_cell<PC, true>(P, x, c, false);
   Thermo th;
   double tgasold = 0.0;
   cool_rate<PC>(P, c, true, tgasold, th, false);
@@ -258,7 +266,7 @@ __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubS
     // solve_rate_cool_g.F:554-646
     if (fabs(dedot) < GRB_TINY8) dedot = dmin(GRB_TINY, c.de);
     if (fabs(HIdot) < GRB_TINY8) HIdot = dmin(GRB_TINY, c.HI);
-    if (dmin(fabs(RK(k1) * c.de * c.HI), fabs(RK(k2) * c.HII * c.de)) / dmax(fabs(dedot), fabs(HIdot)) > 1.0e6) {
+    if (dmin(fabs(RK(k1) * c.de * c.HI), fabs(RK(k2) * c.HII * c.de)) > 1.0e6 * dmax(fabs(dedot), fabs(HIdot))) {
       dedot = GRB_TINY8;
       HIdot = GRB_TINY8;
     }
@@ -266,7 +274,8 @@ __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubS
       dedot = dmin(fabs(dedot), fabs(s.dedot_prev));
       HIdot = dmin(fabs(HIdot), fabs(s.HIdot_prev));
     }
-    dtit = dmin(dmin(fabs(0.1 * c.de / dedot), fabs(0.1 * c.HI / HIdot)), dmin(dt - s.ttot, 0.5 * dt));
+    // (after iter > 50 either rate can be exactly zero: the quotient must be +Inf then)
+    dtit = dmin(dmin(fabs(ddiv_s(0.1 * c.de, dedot)), fabs(ddiv_s(0.1 * c.HI, HIdot))), dmin(dt - s.ttot, 0.5 * dt));
 
     if (PC > 1 && c.d * P.dom > 1e8 && edot > 0.0) {
       // keep the 3-body equilibrium H abundance from changing by more than 10 %
@@ -276,29 +285,29 @@ __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubS
       const double k22lo = ld(P.k22a + ridx - 1), k22hi = ld(P.k22a + ridx);
       const double k13lo = ld(P.k13a + ridx - 1), k13hi = ld(P.k13a + ridx);
       const double eqt2 = dmin(th.logtgas + 0.1 * P.dlogtem, lt2);
-      double eqtdef = (eqt2 - lt1) / (lt2 - lt1);
+      double eqtdef = (eqt2 - lt1) * P.inv_dlogtem;
       const double eqk222 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk132 = k13lo + (k13hi - k13lo) * eqtdef;
-      const double heq2 = (-1.0 / (4.0 * eqk222)) * (eqk132 - sqrt(8.0 * eqk132 * eqk222 * fd + eqk132 * eqk132));
+      const double heq2 = ddiv(-1.0, 4.0 * eqk222) * (eqk132 - sqrt(8.0 * eqk132 * eqk222 * fd + eqk132 * eqk132));
       const double eqt1 = dmax(th.logtgas - 0.1 * P.dlogtem, lt1);
-      eqtdef = (eqt1 - lt1) / (lt2 - lt1);
+      eqtdef = (eqt1 - lt1) * P.inv_dlogtem;
       const double eqk221 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk131 = k13lo + (k13hi - k13lo) * eqtdef;
-      const double heq1 = (-1.0 / (4.0 * eqk221)) * (eqk131 - sqrt(8.0 * eqk131 * eqk221 * fd + eqk131 * eqk131));
-      const double dheq = (fabs(heq2 - heq1) / (dexp(eqt2) - dexp(eqt1))) * (th.tgas / th.p2d) * edot;
-      const double heq = (-1.0 / (4.0 * RK(k22))) * (RK(k13) - sqrt(8.0 * RK(k13) * RK(k22) * fd + RK(k13) * RK(k13)));
-      dtit = dmin(dtit, 0.1 * heq / dheq);
+      const double heq1 = ddiv(-1.0, 4.0 * eqk221) * (eqk131 - sqrt(8.0 * eqk131 * eqk221 * fd + eqk131 * eqk131));
+      const double dheq = ddiv(fabs(heq2 - heq1), dexp(eqt2) - dexp(eqt1)) * ddiv(th.tgas, th.p2d) * edot;
+      const double heq = ddiv(-1.0, 4.0 * RK(k22)) * (RK(k13) - sqrt(8.0 * RK(k13) * RK(k22) * fd + RK(k13) * RK(k13)));
+      dtit = dmin(dtit, ddiv(0.1 * heq, dheq));
     }
     // (the reference's iter>10 rule min(1.5*olddtit, dtit) is inert: olddtit is always huge8)
   }
 
   // cooling/heating limit (:698-750)
-  const double energy = dmax(th.p2d / (P.gamma - 1.0), GRB_TINY8);
+  const double energy = dmax(th.p2d * P.inv_gm1, GRB_TINY8);
   if (th.tgas <= 1.01 * P.temstart && edot < 0.0) edot = GRB_TINY8;
   if (fabs(edot) < GRB_TINY8) edot = GRB_TINY8;
-  dtit = dmin(dmin(fabs(0.1 * energy / edot), dt - s.ttot), dtit);
+  dtit = dmin(dmin(fabs(ddiv(0.1 * energy, edot)), dt - s.ttot), dtit);
 
-  if (P.icool == 1) c.e = c.e + edot / c.d * dtit;
+  if (P.icool == 1) c.e = c.e + ddiv(edot, c.d) * dtit;
   if (PC > 0) step_species<PC>(P, c, th, r, dtit, s.HIdot_prev, s.dedot_prev);
 
   s.ttot = dmin(s.ttot + dtit, dt);
@@ -445,7 +454,7 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
             const bool lit = P.f[F_KPHHI][x] > 0;
             run = (P.iradstep == 1) ? lit : !lit;
           }
-          load_cell<PC>(P, x, c, true);
+          load_cell<PC, false>(P, x, c, true);
           s.ttot = 0.0; s.tgasold = 0.0; s.dedot_prev = 0.0; s.HIdot_prev = 0.0; s.iter = 1;
           if (run) active = true;
           else store_cell<PC>(P, x, c);     // masked cell: floors + consistency only

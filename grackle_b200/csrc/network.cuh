@@ -206,7 +206,7 @@ __device__ inline void rate_derivs(const GrParams &P, const Cell &c, const Therm
             + (RS(k24s) * HI + RS(k25s) * HeII / 4.0 + RS(k26s) * HeI / 4.0);
 
     // H2 formation heating, Omukai (2000) eq. 23
-    const double h2heatfac = drcp(1.0 + ddiv(RK(ncrn), P.dom * (HI * RK(ncrd1) + H2I * 0.5 * RK(ncrd2))));
+    const double h2heatfac = ddiv_s(1.0, 1.0 + ddiv_s(RK(ncrn), P.dom * (HI * RK(ncrd1) + H2I * 0.5 * RK(ncrd2))));
     double H2delta = HI * (4.48 * RK(k22) * (HI * HI) - 4.48 * RK(k13) * H2I / 2.0);
     if (H2delta > 0.0) H2delta = H2delta * h2heatfac;
     if (anydust) H2delta = H2delta + RS(h2dust) * HI * th.rhoH * (0.2 + 4.2 * h2heatfac);
@@ -293,7 +293,7 @@ __device__ inline void step_species(const GrParams &P, Cell &c, const Thermo &th
     if (rt_honly) scoef = scoef + kphHI * HIp;
     acoef = -(RK(k1) * HI - RK(k2) * HII + RK(k3) * HeI / 4.0 - RK(k6) * HeIII / 4.0 + RK(k5) * HeII / 4.0 -
               RK(k4) * HeII / 4.0 + RK(k14) * HM - RK(k7) * HI - RK(k18) * H2II / 2.0);
-    dep = (scoef * dt + de) / (1.0 + acoef * dt);
+    dep = ddiv(scoef * dt + de, 1.0 + acoef * dt);
 
     scoef = 2.0 * (RK(k8) * HM * HI + RK(k10) * H2II * HI / 2.0 + RK(k19) * H2II * HM / 2.0 +
                    RK(k22) * HI * (HI * HI));
@@ -364,16 +364,16 @@ __device__ inline void make_consistent(const GrParams &P, Cell &c)
     c.HM = fabs(c.HM); c.H2II = fabs(c.H2II); c.H2I = fabs(c.H2I);
     totalH = totalH + c.HM + c.H2I + c.H2II;
   }
-  const double correctH = P.fh * metalfree / totalH;
+  const double correctH = ddiv(P.fh * metalfree, totalH);
   c.HI = c.HI * correctH;
   c.HII = c.HII * correctH;
-  const double correctHe = (1.0 - P.fh) * metalfree / totalHe;
+  const double correctHe = ddiv((1.0 - P.fh) * metalfree, totalHe);
   c.HeI = c.HeI * correctHe; c.HeII = c.HeII * correctHe; c.HeIII = c.HeIII * correctHe;
   if (PC > 1) { c.HM = c.HM * correctH; c.H2II = c.H2II * correctH; c.H2I = c.H2I * correctH; }
   if (PC > 2) {
     c.DI = fabs(c.DI); c.DII = fabs(c.DII); c.HDI = fabs(c.HDI);
     const double totalD = c.DI + c.DII + 2.0 / 3.0 * c.HDI;
-    const double correctD = P.fh * P.dtoh * metalfree / totalD;
+    const double correctD = ddiv(P.fh * P.dtoh * metalfree, totalD);
     c.DI = c.DI * correctD; c.DII = c.DII * correctD; c.HDI = c.HDI * correctD;
   }
   c.de = c.HII + c.HeII / 4.0 + c.HeIII / 2.0;

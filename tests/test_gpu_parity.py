@@ -167,6 +167,20 @@ def test_compact_and_general_solve_kernels_agree(pairs, synth_table, product_lib
         assert close.mean() > 0.85, (k, close.mean())
 
 
+def test_fastmath_on_device():
+    """fastmath.cuh on the device (MUFU.RCP64H seed) against the CUDA library functions over
+    10^-300..10^300; the binary is built by __graft_entry__.build()"""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "bin", "fastmath_gpu")
+    assert os.path.exists(exe), "run __graft_entry__.build() first"
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    rows = {ln.split()[0]: ln.split()[1:] for ln in out.stdout.strip().splitlines()}
+    assert float(rows["div"][0]) <= 2.3e-16 and float(rows["rcp"][0]) <= 2.3e-16
+    assert float(rows["log"][0]) <= 1e-15 and float(rows["exp"][0]) <= 1e-15 and float(rows["exp10"][0]) <= 1e-15
+
+
 def test_conservation_after_solve(pairs, synth_table):
     """make_consistent: H, He (and D) species sum to fh*(rho-metal) etc. after the call"""
     cp, co, dt = pairs["C4"]
