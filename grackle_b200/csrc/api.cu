@@ -126,7 +126,7 @@ int upload_tables(DeviceCtx *ctx, const chemistry_data *chem, const chemistry_da
   ctx->ndratec = chem->NumberOfDustTemperatureBins;
 
   if (chem->primordial_chemistry > 0) {
-    std::vector<double> m((size_t)nb * NCHEM, 0.0);
+    std::vector<double> m((size_t)nb * NCHEM * 2, 0.0);     // (value, next - value) pairs
     const double *cols[NCHEM] = {nullptr};
     cols[C_k1] = r->k1; cols[C_k2] = r->k2; cols[C_k3] = r->k3; cols[C_k4] = r->k4;
     cols[C_k5] = r->k5; cols[C_k6] = r->k6; cols[C_k57] = r->k57; cols[C_k58] = r->k58;
@@ -140,14 +140,17 @@ int upload_tables(DeviceCtx *ctx, const chemistry_data *chem, const chemistry_da
     cols[C_k54] = r->k54; cols[C_k55] = r->k55; cols[C_k56] = r->k56;
     for (int c = 0; c < NCHEM; c++)
       if (cols[c])
-        for (int b = 0; b < nb; b++) m[(size_t)b * NCHEM + c] = cols[c][b];
+        for (int b = 0; b < nb; b++) {
+          m[((size_t)b * NCHEM + c) * 2] = cols[c][b];
+          m[((size_t)b * NCHEM + c) * 2 + 1] = (b + 1 < nb) ? cols[c][b + 1] - cols[c][b] : 0.0;
+        }
     if (upload(&ctx->chem, m.data(), m.size()) == GR_FAIL) return GR_FAIL;
     if (upload(&ctx->k13a, r->k13, nb) == GR_FAIL) return GR_FAIL;
     if (upload(&ctx->k22a, r->k22, nb) == GR_FAIL) return GR_FAIL;
     if (upload(&ctx->h2dust, r->h2dust, (size_t)nb * ctx->ndratec) == GR_FAIL) return GR_FAIL;
   }
   {
-    std::vector<double> m((size_t)nb * NCOOL, 0.0);
+    std::vector<double> m((size_t)nb * NCOOL * 2, 0.0);
     const double *cols[NCOOL] = {nullptr};
     cols[L_CEHI] = r->ceHI; cols[L_CEHEI] = r->ceHeI; cols[L_CEHEII] = r->ceHeII;
     cols[L_CIHI] = r->ciHI; cols[L_CIHEI] = r->ciHeI; cols[L_CIHEIS] = r->ciHeIS;
@@ -159,7 +162,10 @@ int upload_tables(DeviceCtx *ctx, const chemistry_data *chem, const chemistry_da
     cols[L_REGR] = r->regr;
     for (int c = 0; c < NCOOL; c++)
       if (cols[c])
-        for (int b = 0; b < nb; b++) m[(size_t)b * NCOOL + c] = cols[c][b];
+        for (int b = 0; b < nb; b++) {
+          m[((size_t)b * NCOOL + c) * 2] = cols[c][b];
+          m[((size_t)b * NCOOL + c) * 2 + 1] = (b + 1 < nb) ? cols[c][b + 1] - cols[c][b] : 0.0;
+        }
     if (upload(&ctx->cool, m.data(), m.size()) == GR_FAIL) return GR_FAIL;
   }
   if (upload_cloudy(ctx->pri, r->cloudy_primordial) == GR_FAIL) return GR_FAIL;

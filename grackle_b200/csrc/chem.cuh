@@ -20,33 +20,25 @@ struct Thermo {
   double logtgas;     // ln(tgas), formed once here and reused by the rate lookup
 };
 
-// two adjacent rows of a packed table -> lerp of column `col`
-// cooling tables: a + t*(b-a) (cool1d_multi_g.F:387-410); rate tables: a + (b-a)*t
-// (solve_rate_cool_g.F:1225-1240).  Both spellings round identically.
-__device__ __forceinline__ double lerp_row(const double *row, int ncol, int col, double t)
+// One row of a packed table holds (value, difference to the next bin) pairs: column `col`
+// interpolated at weight t is a + d * t - the reference's a + (b - a) * t
+// (cool1d_multi_g.F:387-410, solve_rate_cool_g.F:1225-1240) with b - a formed on the host.
+__device__ __forceinline__ double lerp_row(const double *row, int col, double t)
 {
-  const double a = ld(row + col), b = ld(row + ncol + col);
-  return a + (b - a) * t;
+  const double2 p = __ldg(reinterpret_cast<const double2 *>(row) + col);
+  return p.x + p.y * t;
 }
 
-// N (even) consecutive columns starting at the even column C0: all 2*N/2 double2 loads are
-// issued before the first lerp, so a cell pays ONE table round trip per column group
-// instead of one per column (ncu round 1: 77 % of the long-scoreboard stall cycles sat on
-// the dependent DADD of the one-at-a-time lerp).
-template <int NCOL, int C0, int N>
+// N consecutive columns starting at C0: all loads are issued before the first use
+template <int C0, int N>
 __device__ __forceinline__ void lerp_cols(const double *row, double t, double (&out)[N])
 {
-  static_assert((C0 % 2) == 0 && (N % 2) == 0 && (NCOL % 2) == 0, "double2 alignment");
-  double2 a[N / 2], b[N / 2];
-  const double2 *p0 = reinterpret_cast<const double2 *>(row + C0);
-  const double2 *p1 = reinterpret_cast<const double2 *>(row + NCOL + C0);
+  double2 p[N];
+  const double2 *q = reinterpret_cast<const double2 *>(row) + C0;
 #pragma unroll
-  for (int i = 0; i < N / 2; i++) { a[i] = __ldg(p0 + i); b[i] = __ldg(p1 + i); }
+  for (int i = 0; i < N; i++) p[i] = __ldg(q + i);
 #pragma unroll
-  for (int i = 0; i < N / 2; i++) {
-    out[2 * i] = a[i].x + (b[i].x - a[i].x) * t;
-    out[2 * i + 1] = a[i].y + (b[i].y - a[i].y) * t;
-  }
+  for (int i = 0; i < N; i++) out[i] = p[i].x + p[i].y * t;
 }
 
 // Rahmati+13 eq. 13/14 shielding fraction (cool1d_multi_g.F:788-792, solve_rate_cool_g.F:1518-1520)
@@ -300,30 +292,30 @@ __device__ inline void cool_rate(const GrParams &P, const Cell &c, bool first, d
   double tdef = 0.0;
   if ((PC > 0) || (P.idustall > 0)) {
     const TIndex ti = t_index(P, logtem);
-    row = P.cool + (size_t)(ti.idx - 1) * NCOOL;
+    row = P.cool + (size_t)(ti.idx - 1) * (NCOOL * 2);
     tdef = ti.tdef;
   }
   if (PC > 0) {
     double at[12];
-    lerp_cols<NCOOL, L_CEHI, 12>(row, tdef, at);
+    lerp_cols<L_CEHI, 12>(row, tdef, at);
 #pragma unroll
     for (int i = 0; i < 12; i++) cv.v[L_CEHI + i] = at[i];
   }
   if (PC > 1) {
     double ga[6];
-    lerp_cols<NCOOL, L_GAHI, 6>(row, tdef, ga);
+    lerp_cols<L_GAHI, 6>(row, tdef, ga);
 #pragma unroll
     for (int i = 0; i < 6; i++) cv.v[L_GAHI + i] = ga[i];
-    if (P.iciecool == 1) cv.v[L_CIECO] = lerp_row(row, NCOOL, L_CIECO, tdef);
+    if (P.iciecool == 1) cv.v[L_CIECO] = lerp_row(row, L_CIECO, tdef);
   }
   if (PC > 2) {
     double hd[2];
-    lerp_cols<NCOOL, L_HDLTE, 2>(row, tdef, hd);
+    lerp_cols<L_HDLTE, 2>(row, tdef, hd);
     cv.v[L_HDLTE] = hd[0]; cv.v[L_HDLOW] = hd[1];
   }
   if (anydust) {
-    cv.v[L_GASGR] = lerp_row(row, NCOOL, L_GASGR, tdef);
-    cv.v[L_REGR] = lerp_row(row, NCOOL, L_REGR, tdef);
+    cv.v[L_GASGR] = lerp_row(row, L_GASGR, tdef);
+    cv.v[L_REGR] = lerp_row(row, L_REGR, tdef);
   }
   cool_sums<PC>(P, c, logtem, cv, tgasold, th);
 }

@@ -5,12 +5,13 @@
 //  * Fields: the caller's SoA arrays, untouched layout (i fastest).  One thread owns
 //    one active cell; a warp reads 32 consecutive i => 256-byte coalesced segments.
 //  * Per-T tables: re-packed from the reference's 70 separate 600-entry arrays
-//    (chemistry_data_storage) into two row-major matrices
-//        chem[bin][NCHEM]   (k1..k58, ncr*, k13dd*14)      600 x 48 doubles = 230 KB
-//        cool[bin][NCOOL]   (ceHI..brem, GA*, H2LTE, ...)  600 x 24 doubles = 115 KB
-//    so the two bins a cell interpolates between are ONE contiguous span
-//    (2 x 384 B resp. 2 x 192 B) instead of 92 scattered 8-byte gathers; in the solve kernel a
-//    group of lanes reads that span coalesced (one double2 piece per lane).
+//    (chemistry_data_storage) into two row-major matrices of (value, difference to the next
+//    bin) pairs, so that an interpolation is ONE 16-byte load and ONE fused multiply-add,
+//    v = a + d * t with d = v[bin+1] - v[bin] formed on the host (bitwise what the subtraction
+//    in the kernel would give), and a cell needs a single contiguous row:
+//        chem[bin][NCHEM][2]   (k1..k58, ncr*, k50..k56 | k13dd*14)   600 x 768 B = 461 KB
+//        cool[bin][NCOOL][2]   (ceHI..brem, GA*, H2LTE, ...)          600 x 384 B = 230 KB
+//    In the solve kernel a group of lanes reads a cell's row coalesced (coop_fetch).
 //  * h2dust[dustbin][bin] (1.2 MB) and the Cloudy grids stay in the reference's
 //    order (T fastest) and are read through the read-only path (L2-resident).
 #ifndef GRB200_DEVICE_H
@@ -18,9 +19,9 @@
 
 #include <cstdint>
 
-// column indices of the packed chemistry-rate matrix.  A row is 48 doubles = 384 B = three
-// 128-byte lines: columns [0,32) are the rates every subcycle needs (two lines), columns
-// [32,46) the 14 Martin+96 coefficients of the density-dependent k13 (one line).  The solve
+// column indices of the packed chemistry-rate matrix.  A row is 48 (value, difference) pairs =
+// 768 B = six 128-byte lines: columns [0,32) are the rates every subcycle needs (four lines),
+// columns [32,46) the 14 Martin+96 coefficients of the density-dependent k13 (two lines).  The solve
 // kernel fetches a cell's two adjacent rows warp-cooperatively (kernels.cu: coop_fetch), a
 // group of lanes reading one cell's row pair as consecutive double2 pieces.
 enum {
@@ -32,10 +33,10 @@ enum {
   C_PAD0 = C_K13DD0 + 14, C_PAD1,
   NCHEM
 };
-static_assert(NCHEM == 48 && C_K13DD0 == 32 && C_k50 == 25, "packed chemistry row is 48 doubles");
+static_assert(NCHEM == 48 && C_K13DD0 == 32 && C_k50 == 25, "packed chemistry row is 48 pairs");
 #define GRB_NCHEM_MAIN 32
 
-// column indices of the packed cooling-rate matrix (24 doubles = 192 B per row)
+// column indices of the packed cooling-rate matrix (24 pairs = 384 B per row)
 enum {
   L_CEHI = 0, L_CEHEI, L_CEHEII, L_CIHI, L_CIHEI, L_CIHEIS, L_CIHEII,
   L_REHII, L_REHEII1, L_REHEII2, L_REHEIII, L_BREM,              // [0,12)  atomic
@@ -44,7 +45,7 @@ enum {
   L_CIECO, L_GASGR, L_REGR, L_PAD,
   NCOOL
 };
-static_assert(NCOOL == 24, "packed cooling row is 24 doubles");
+static_assert(NCOOL == 24, "packed cooling row is 24 pairs");
 
 struct GrCloudyDev {
   long long rank;
@@ -104,8 +105,8 @@ struct GrParams {
   // Rahmati+13 cell-invariant factors: 6.73e-3*(sig/2.49e-18)^(-2/3) and (k/tbase1/1e-12)^(2/3)
   double ssh_sig_hi, ssh_sig_hei, ssh_k24, ssh_k26;
   // tables
-  const double *chem;      // [nratec][NCHEM]
-  const double *cool;      // [nratec][NCOOL]
+  const double *chem;      // [nratec][NCHEM][2]  (value, next - value)
+  const double *cool;      // [nratec][NCOOL][2]
   const double *h2dust;    // [ndratec][nratec]
   const double *k13a;      // raw k13, k22 columns for the H-equilibrium limiter (:606-630)
   const double *k22a;

@@ -209,8 +209,8 @@ __global__ void __launch_bounds__(128) k_dust_temperature(const __grid_constant_
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
   const TIndex ti = t_index(P, logtem);
-  const double *row = P.cool + (size_t)(ti.idx - 1) * NCOOL;
-  double gasgr = lerp_row(row, NCOOL, L_GASGR, ti.tdef);
+  const double *row = P.cool + (size_t)(ti.idx - 1) * (NCOOL * 2);
+  double gasgr = lerp_row(row, L_GASGR, ti.tdef);
   gasgr = gasgr * P.fgr * P.coolunit / GRB_MASS_H;
   P.out[x] = dust_temperature(tgas, nh, gasgr, P.gamma_isrfa, myisrf, P.comp2);
 }
@@ -365,6 +365,16 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 #ifndef GRB_GROUP_WARPS
 #define GRB_GROUP_WARPS 8
 #endif
+// lanes per cell in the cooperative table fetches (fewer lanes = more loads per lane and pass)
+#ifndef GRB_G_MAIN
+#define GRB_G_MAIN 8
+#endif
+#ifndef GRB_G_COOL
+#define GRB_G_COOL 8
+#endif
+#ifndef GRB_G_DD
+#define GRB_G_DD 4
+#endif
 
 static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0, "CTA must be whole lockstep groups");
 static_assert(GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15, "named barriers 1..15");
@@ -382,39 +392,38 @@ __device__ __forceinline__ bool group_any(int bar_id, bool pred)
 }
 
 // Warp-cooperative fetch of one table segment for the 32 cells a warp owns.
-//   table   first column of the segment in row 0 (16-byte aligned)
-//   ROWB    bytes per table row
-//   my_off  THIS lane's cell: byte offset of its lower row; my_t: its interpolation weight
+//   table   first (value, difference) pair of the segment in row 0
+//   ROWB    bytes per table row;  NCOLS columns in the segment
+//   my_off  THIS lane's cell: byte offset of its row; my_t: its interpolation weight
 //   dst0    this warp's lane-0 slot row + the segment's first slot
-// G lanes serve one cell per pass (32/G cells per pass, G passes): lane g < NP of a group
-// loads the double2 piece g of the cell's lower and upper row - the group's loads are
-// consecutive 16-byte words of one or two 128-byte lines - interpolates a + (b - a) * t
-// (solve_rate_cool_g.F:1225-1320, cool1d_multi_g.F:387-410) and stores columns 2g / 2g+1 to
-// slots g / NP+g of that cell's row.  All 2*G loads are independent, so the compiler keeps
-// as many in flight as registers allow.
-template <int G, int NP, int ROWB>
+// G lanes serve one cell per pass (32/G cells per pass, G passes): lane g of a group loads the
+// pairs of columns g, g+G, g+2G, ... - each load instruction of the group covers G
+// consecutive 16-byte words - forms a + d * t and stores column c to slot c of that cell's row.
+// All loads of a pass are independent of each other.
+// (explicit load batches over passes and a group barrier only every 2nd/4th subcycle were
+// measured slower than letting the compiler schedule this loop.)
+template <int G, int NCOLS, int ROWB>
 __device__ __forceinline__ void coop_fetch(const double *table, int my_off, double my_t, double *dst0)
 {
-  static_assert(G == 4 || G == 8 || G == 16, "lanes per cell");
-  static_assert(NP <= G, "pieces per cell");
+  static_assert(G == 2 || G == 4 || G == 8 || G == 16, "lanes per cell");
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int g = lane & (G - 1), sub = lane / G;
-  constexpr int CPP = 32 / G;      // cells per pass
+  constexpr int CPP = 32 / G;                 // cells per pass
+  constexpr int PER = (NCOLS + G - 1) / G;    // columns per lane
   const char *src = reinterpret_cast<const char *>(table) + 16 * g;
   double *dst = dst0 + sub * GRB_SLOT_STRIDE + g;
-  // (explicit load batches of 2/4/8 passes and a group barrier only every 2nd/4th subcycle
-  // were measured slower than this plain loop: 12.2/11.9/11.6 and 10.9/9.5 vs 12.6 Mcell/s)
 #pragma unroll
   for (int pass = 0; pass < G; pass++) {
     const int cell = pass * CPP + sub;
     const int off = __shfl_sync(full, my_off, cell);
     const double t = __shfl_sync(full, my_t, cell);
-    if (NP == G || g < NP) {
-      const double2 a = __ldg(reinterpret_cast<const double2 *>(src + off));
-      const double2 b = __ldg(reinterpret_cast<const double2 *>(src + off + ROWB));
-      dst[pass * CPP * GRB_SLOT_STRIDE] = a.x + (b.x - a.x) * t;
-      dst[pass * CPP * GRB_SLOT_STRIDE + NP] = a.y + (b.y - a.y) * t;
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+      if ((k + 1) * G <= NCOLS || g + k * G < NCOLS) {
+        const double2 p = __ldg(reinterpret_cast<const double2 *>(src + off + 16 * k * G));
+        dst[pass * CPP * GRB_SLOT_STRIDE + k * G] = p.x + p.y * t;
+      }
     }
   }
 }
@@ -478,21 +487,21 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
       logtem = thermo_head<PC>(P, c, s.iter == 1, s.tgasold, th, true);
       if ((PC > 0) || (P.idustall > 0)) {           // cool1d_multi_g.F:349-357
         const TIndex ta = t_index(P, logtem);
-        offA = (ta.idx - 1) * (NCOOL * 8);
+        offA = (ta.idx - 1) * (NCOOL * 16);
         tdefA = ta.tdef;
       }
       if (PC > 0) {                                 // solve_rate_cool_g.F:1211-1222
         double lt = dmax(th.logtgas, P.logtem0);
         lt = dmin(lt, P.logtem9);
         tb = t_index(P, lt);
-        offB = (tb.idx - 1) * (NCHEM * 8);
+        offB = (tb.idx - 1) * (NCHEM * 16);
       }
     }
     // stage 2 (warp): cooling rows and the k13dd coefficients -> slots
-    if (PC > 0) coop_fetch<8, 8, NCOOL * 8>(P.cool, offA, tdefA, warp_slots + SLA_COOL0);
-    if (PC > 1 || anydust) coop_fetch<4, 4, NCOOL * 8>(P.cool + 16, offA, tdefA, warp_slots + SLA_COOL1);
+    if (PC > 1 || anydust) coop_fetch<GRB_G_COOL, NCOOL, NCOOL * 16>(P.cool, offA, tdefA, warp_slots + SLA_COOL);
+    else if (PC == 1) coop_fetch<4, L_BREM + 1, NCOOL * 16>(P.cool, offA, tdefA, warp_slots + SLA_COOL);
     if (PC > 1 && P.ithreebody == 0)
-      coop_fetch<8, 7, NCHEM * 8>(P.chem + C_K13DD0, offB, tb.tdef, warp_slots + SLA_DD);
+      coop_fetch<GRB_G_DD, 14, NCHEM * 16>(P.chem + 2 * C_K13DD0, offB, tb.tdef, warp_slots + SLA_DD);
     __syncwarp();
     // stage 3 (per cell): cooling / heating sums, density-dependent k13
     double k13dd = GRB_TINY8;
@@ -503,9 +512,8 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
     __syncwarp();
     if (PC > 0) {
       // stage 4 (warp): chemistry rows -> slots
-      if (PC == 1) coop_fetch<4, 4, NCHEM * 8>(P.chem, offB, tb.tdef, warp_slots);
-      else if (PC == 2) coop_fetch<16, 13, NCHEM * 8>(P.chem, offB, tb.tdef, warp_slots);
-      else coop_fetch<16, 16, NCHEM * 8>(P.chem, offB, tb.tdef, warp_slots);
+      if (PC == 1) coop_fetch<4, chem_cols(1), NCHEM * 16>(P.chem, offB, tb.tdef, warp_slots);
+      else coop_fetch<GRB_G_MAIN, chem_cols(PC), NCHEM * 16>(P.chem, offB, tb.tdef, warp_slots);
       __syncwarp();
       // stage 5 (per cell): shielding, H2 on dust
       if (active) subcycle_lookup<PC>(P, c, th, x, tb, k13dd, r);

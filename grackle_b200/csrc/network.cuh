@@ -11,40 +11,31 @@ namespace grb {
 // The interpolated rates of one cell-subcycle live in SHARED memory (a row of GRB_SLOT_STRIDE
 // doubles per thread; the odd stride makes a warp's accesses to one slot conflict-free).  The
 // rows are FILLED warp-cooperatively (kernels.cu: coop_fetch): a group of G lanes reads one
-// cell's two adjacent table rows as consecutive double2 pieces - coalesced, one L1 wavefront
-// per 128-byte line instead of one per lane - interpolates, and stores into that cell's row.
-// Piece g of a segment of NP pieces holds columns (2g, 2g+1); they land in slots
-// base+g and base+NP+g so that the lanes of a group store to consecutive words.
+// cell's table row as consecutive 16-byte (value, difference) pairs - coalesced, one L1
+// wavefront per 128-byte line instead of one per lane - interpolates, and stores into that
+// cell's row, column c of a segment going to slot base + c.
 //
-// Slot map.  Phase A (before the cooling sums): cooling columns [0,16) -> slots [0,16),
-// cooling columns [16,24) -> [16,24), the 14 k13dd columns -> [24,38).  Phase B (before the
-// species update) overwrites them: chemistry columns [0,32) -> slots [0,32), then the slots
-// the lookup itself produces.
+// Slot map.  Phase A (before the cooling sums): the 24 cooling columns -> slots [0,24), the 14
+// k13dd columns -> [24,38).  Phase B (before the species update) overwrites them: chemistry
+// columns [0,32) -> slots [0,32), followed by the slots the lookup itself produces.
 #define GRB_SLOT_STRIDE 41
 enum { SL_h2dust = GRB_NCHEM_MAIN, SL_k24s, SL_k25s, SL_k26s, SL_k28s, SL_k29s, SL_k30s, SL_k31s, NSLOT };
 static_assert(NSLOT <= GRB_SLOT_STRIDE && (GRB_SLOT_STRIDE & 1) == 1, "slot row");
-enum { SLA_COOL0 = 0, SLA_COOL1 = 16, SLA_DD = 24 };
+enum { SLA_COOL = 0, SLA_DD = NCOOL };
+static_assert(SLA_DD + 16 <= GRB_SLOT_STRIDE, "phase A slots");
 
-// pieces of the chemistry row the network PC needs every subcycle
-__host__ __device__ constexpr int chem_pieces(int pc) { return pc == 1 ? 4 : (pc == 2 ? 13 : 16); }
-template <int PC>
-__host__ __device__ constexpr int chem_slot(int col) { return (col >> 1) + (col & 1) * chem_pieces(PC); }
-__host__ __device__ constexpr int cool_slot(int col)
-{
-  return col < 16 ? SLA_COOL0 + (col >> 1) + (col & 1) * 8 : SLA_COOL1 + ((col - 16) >> 1) + (col & 1) * 4;
-}
-__host__ __device__ constexpr int dd_slot(int n) { return SLA_DD + (n >> 1) + (n & 1) * 7; }
-static_assert(2 * chem_pieces(1) > C_k58 && 2 * chem_pieces(2) > C_ncrd2 && 2 * chem_pieces(3) > C_k56, "chem pieces");
+// chemistry columns the network PC needs every subcycle
+__host__ __device__ constexpr int chem_cols(int pc) { return pc == 1 ? C_k58 + 1 : (pc == 2 ? C_ncrd2 + 1 : C_k56 + 1); }
 
 struct Rates {
   double *base;    // this thread's slot row in shared memory
 };
-#define RK(name) (r.base[chem_slot<PC>(C_##name)])
+#define RK(name) (r.base[C_##name])
 #define RS(name) (r.base[SL_##name])
 // cooling-table values read back from the slots (phase A)
 struct CoolSlots {
   const double *base;
-  __device__ __forceinline__ double operator()(int col) const { return base[cool_slot(col)]; }
+  __device__ __forceinline__ double operator()(int col) const { return base[SLA_COOL + col]; }
 };
 
 // neighbour densities for the Sobolev-like H2 shielding length (H2_self_shielding == 1)
@@ -61,7 +52,7 @@ __device__ inline double k13_martin(const GrParams &P, const Cell &c, const Ther
   const double nh = dmin(c.HI * P.dom, 1.0e9);
   double k13 = GRB_TINY8;
   if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
-#define DD(n) (slots[dd_slot(n)])
+#define DD(n) (slots[SLA_DD + (n)])
     double cid = DD(0) - ddiv(DD(1), 1.0 + pow_pos(ddiv(nh, DD(4)), DD(6))) + DD(2) -
                  ddiv(DD(3), 1.0 + pow_pos(ddiv(nh, DD(5)), DD(6)));
     cid = dmax(dexp10(cid), GRB_TINY8);
