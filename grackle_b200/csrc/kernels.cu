@@ -363,7 +363,7 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 // barrier: inside a group one warp's instruction fetch serves all, while the groups run out
 // of phase with each other so one group's barrier tail is covered by the others' work.
 #ifndef GRB_GROUP_WARPS
-#define GRB_GROUP_WARPS 8
+#define GRB_GROUP_WARPS 4
 #endif
 // lanes per cell in the cooperative table fetches (fewer lanes = more loads per lane and pass)
 #ifndef GRB_G_MAIN
@@ -377,7 +377,7 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 #endif
 
 static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0, "CTA must be whole lockstep groups");
-static_assert(GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15, "named barriers 1..15");
+static_assert(GRB_GROUP_WARPS == 1 || GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15, "named barriers 1..15");
 
 // barrier + OR-reduction of a predicate over the group
 __device__ __forceinline__ bool group_any(int bar_id, bool pred)
@@ -473,7 +473,7 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
       }
     }
     // after the refill every lane either owns a cell or has seen the end of the queue
-    if (!group_any(bar_id, active)) break;
+    if (GRB_GROUP_WARPS == 1 ? !__any_sync(full, active) : !group_any(bar_id, active)) break;
 
     // ---- one subcycle on every busy lane ----
     // stage 1 (per cell): temperature and the two log-T bins.  Idle lanes point at bin 1.
