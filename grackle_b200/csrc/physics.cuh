@@ -23,8 +23,22 @@ namespace grb {
 // 1/ln(10) as the reference forms it: 1._DKIND / log(10._DKIND) (cool1d_cloudy_g.F:107)
 #define GRB_INV_LN10 (1.0 / 2.302585092994046)
 
-__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
-__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+// min / max with the Fortran-like "a < b ? a : b" meaning, spelled in PTX: written in C the
+// compiler turns a comparison against a constant into max.f64 / min.f64, whose NaN-aware
+// expansion is 9 instructions on sm_100a instead of these 3 (DSETP + 2 FSEL); the species
+// floors alone are 12 of them per subcycle.
+__device__ __forceinline__ double dmin(double a, double b)
+{
+  double r;
+  asm("{\n\t.reg .pred p;\n\tsetp.lt.f64 p, %1, %2;\n\tselp.f64 %0, %1, %2, p;\n\t}" : "=d"(r) : "d"(a), "d"(b));
+  return r;
+}
+__device__ __forceinline__ double dmax(double a, double b)
+{
+  double r;
+  asm("{\n\t.reg .pred p;\n\tsetp.gt.f64 p, %1, %2;\n\tselp.f64 %0, %1, %2, p;\n\t}" : "=d"(r) : "d"(a), "d"(b));
+  return r;
+}
 __device__ __forceinline__ long long imin(long long a, long long b) { return a < b ? a : b; }
 __device__ __forceinline__ long long imax(long long a, long long b) { return a > b ? a : b; }
 __device__ __forceinline__ double ld(const double *p) { return __ldg(p); }
