@@ -34,6 +34,7 @@ SLAB = (1024, 1024, 128)            # (ni, nj, nk) per GPU
 BYTES_PER_CELL = 224                # 15 fields read + 13 written, FP64
 FLOP_PER_SUBCYCLE = 1050.0          # SURVEY 8d hand count for C4 (a5 360 + a7 170 + a8 185 + a9 340)
 FLOP_PER_CELL_FIXED = 60.0          # scale + ceiling + make_consistent
+TRAFFIC_PER_CELL_NCU = 219.3        # (dram__bytes_read + dram__bytes_write) / cells, profiles/r1_solve_v7_summary.txt
 
 
 def load_peaks():
@@ -150,7 +151,7 @@ def run_reference(args):
         "config": {"workload": "C4 pc=3 + metal_cooling + UVB, comoving z=3, Set B, dt=1 Myr; CPU sample "
                                "%dx%dx%d cells of the 1024x1024x128 slab" % dims,
                    "tables": "synthetic HM2012-schema", "mean_subcycles_per_cell": sub},
-        "cpu_baseline": {"value": rate, "unit": "cells/s", "cores": cores, "kind": "reference",
+        "cpu_baseline": {"value": rate, "unit": "cells/s", "cores": cores, "kind": "port",
                          "sample": "%dx%dx%d cells, reference C glue + C++ restatement of its Fortran "
                                    "(no Fortran compiler on this image), OpenMP guided,1" % dims},
         "e2e": {"value": rate, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -250,21 +251,50 @@ def run_ours(args):
     value = world * ncell * args.steps / elapsed
 
     # ---- roofline of the dominant kernel (k_solve), from its own CUDA-event times ----
+    # The solve is bound by the FP64 pipe, not by HBM or tensor cores (there is no dense
+    # contraction on this path): `roofline` is therefore quoted against the measured non-tensor
+    # FP64 FMA peak, and the HBM view of the same kernel is kept beside it as `roofline_hbm`.
     k_s = float(np.mean(kernel_ms)) * 1e-3
     hbm_peak, peak_kind = load_peaks()
     achieved_gbs = BYTES_PER_CELL * ncell / k_s / 1e9
     flops = subs * FLOP_PER_SUBCYCLE + ncell * FLOP_PER_CELL_FIXED
     fp64_peak = lib.grb200_measure_fp64_tflops()
-    roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": peak_kind,
-                "kernel": "k_solve<3>", "kernel_ms": k_s * 1e3,
-                "note": "solve is FP64-pipe bound (arithmetic intensity %.0f flop/B); see roofline_fp64"
-                        % (flops / (BYTES_PER_CELL * ncell))}
-    roofline_fp64 = {"bound": "fp64", "achieved": flops / k_s / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
-                     "frac": flops / k_s / 1e12 / fp64_peak if fp64_peak > 0 else None,
-                     "peak_source": "FMA-chain microbenchmark in this run (grb200_measure_fp64_tflops)",
-                     "flop_model": "sum(subcycles)*%g + cells*%g (SURVEY 8d hand count)" % (FLOP_PER_SUBCYCLE, FLOP_PER_CELL_FIXED),
-                     "subcycles_per_cell": subs / ncell}
+    roofline = {"bound": "fp64", "achieved": flops / k_s / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+                "frac": flops / k_s / 1e12 / fp64_peak if fp64_peak > 0 else None,
+                # ncu --set full on the 2 Mi-cell sample (profiles/): 220 B/cell of DRAM traffic for
+                # 224 B/cell algorithmic, i.e. no re-reads; scaled to this launch's cells
+                "traffic": TRAFFIC_PER_CELL_NCU * ncell,
+                "traffic_note": "dram__bytes_read+write of k_solve from the ncu capture in profiles/ "
+                                "(%.0f B/cell) x cells of this launch" % TRAFFIC_PER_CELL_NCU,
+                "kernel": "k_solve<3, lean>", "kernel_ms": k_s * 1e3,
+                "peak_source": "FMA-chain microbenchmark in this run (grb200_measure_fp64_tflops); "
+                               "MEASURED_PEAKS.json has no FP64 entry",
+                "flop_model": "sum(subcycles)*%g + cells*%g algorithmic flops (SURVEY 8d hand count; divisions "
+                              "and log/exp count as 1)" % (FLOP_PER_SUBCYCLE, FLOP_PER_CELL_FIXED),
+                "subcycles_per_cell": subs / ncell}
+    roofline_hbm = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": achieved_gbs / hbm_peak, "peak_source": peak_kind,
+                    "note": "224 B/cell algorithmic; arithmetic intensity %.0f flop/B puts the solve far "
+                            "on the compute side" % (flops / (BYTES_PER_CELL * ncell))}
+
+    # ---- calculate_* sweep (config C5, HBM-bound): GB/s of each non-iterative kernel ----
+    sweep = None
+    if not args.no_sweep:
+        out = torch.empty(ncell, dtype=torch.float64, device=dev)
+        for k in names:
+            work[k].copy_(pristine[k])
+        torch.cuda.synchronize()
+        sweep = {}
+        for what, nbytes in (("pressure", 96), ("temperature", 104), ("gamma", 104), ("cooling_time", 128)):
+            ms = []
+            for it in range(4):
+                assert capi.calculate(ch, grid, what, int(out.data_ptr())) == 1
+                if it > 0:
+                    ms.append(lib.grb200_last_kernel_ms(C.byref(ch.rates)))
+            t = float(np.mean(ms)) * 1e-3
+            sweep[what] = {"ms": t * 1e3, "cells_per_s": ncell / t, "bytes_per_cell": nbytes,
+                           "GB/s": nbytes * ncell / t / 1e9, "frac_hbm": nbytes * ncell / t / 1e9 / hbm_peak}
+        del out
 
     # ---- e2e: same call with HOST (pinned) buffers, copies inside the timed region ----
     e2e = None
@@ -306,7 +336,7 @@ def run_ours(args):
     if rank == 0 and not args.no_cpu:
         dims = (128, 128, 8)
         rate, sec, cores, sub = cpu_solve_rate(table, dims, 1, 0)
-        cpu = {"value": rate, "unit": "cells/s", "cores": cores, "kind": "reference",
+        cpu = {"value": rate, "unit": "cells/s", "cores": cores, "kind": "port",
                "sample": "%dx%dx%d cells of the slab (Set B), 1 call, reference C glue + C++ restatement "
                          "of its Fortran, OpenMP guided,1" % dims}
 
@@ -321,7 +351,7 @@ def run_ours(args):
                        "cells_per_gpu": ncell, "tables": "synthetic HM2012-schema (real file absent from the reference snapshot)",
                        "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2" % (ncell * 120 / 1e9),
                        "mean_subcycles_per_cell": subs / ncell},
-            "roofline": roofline, "roofline_fp64": roofline_fp64, "cpu_baseline": cpu, "e2e": e2e,
+            "roofline": roofline, "roofline_hbm": roofline_hbm, "calculate_sweep": sweep, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": sampler.summary(),
             "diagnostics": {"subcycles_sum_all_ranks": int(diag[0].item()) if dist is not None else int(stats.subcycles_sum),
                             "cells_hit_itmax": int(diag[1].item()) if dist is not None else int(stats.cells_hit_itmax),
@@ -342,6 +372,7 @@ def main():
     ap.add_argument("--e2e-nk", type=int, default=16, help="k extent of the host-buffer e2e run")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the calculate_* (C5) timings")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
