@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "grackle.h"
+#include "fastmath.cuh"
 #include "gr_internal.h"
 #include "gr_device.h"
 #include "gr_launch.h"
@@ -38,7 +39,7 @@ struct DeviceCtx {
   int device = -1;
   bool uploaded = false;
   // packed per-T tables
-  double *chem = nullptr, *cool = nullptr, *h2dust = nullptr, *k13a = nullptr, *k22a = nullptr;
+  double *chem = nullptr, *cool = nullptr, *h2dust = nullptr, *k13a = nullptr, *k22a = nullptr, *fm_tab = nullptr;
   int nratec = 0, ndratec = 0;
   // Cloudy grids (device copies) + host-side metadata
   struct Cloudy {
@@ -168,6 +169,11 @@ int upload_tables(DeviceCtx *ctx, const chemistry_data *chem, const chemistry_da
         }
     if (upload(&ctx->cool, m.data(), m.size()) == GR_FAIL) return GR_FAIL;
   }
+  {
+    double tab[GRB_FM_TABLE_DOUBLES];
+    grb::fm_fill_tables(tab);
+    if (upload(&ctx->fm_tab, tab, GRB_FM_TABLE_DOUBLES) == GR_FAIL) return GR_FAIL;
+  }
   if (upload_cloudy(ctx->pri, r->cloudy_primordial) == GR_FAIL) return GR_FAIL;
   if (upload_cloudy(ctx->met, r->cloudy_metal) == GR_FAIL) return GR_FAIL;
 
@@ -217,7 +223,7 @@ void gr_device_detach(const chemistry_data_storage *rates)
     g_ctx.erase(it);
   }
   if (ctx->uploaded) {
-    cudaFree(ctx->chem); cudaFree(ctx->cool); cudaFree(ctx->h2dust); cudaFree(ctx->k13a); cudaFree(ctx->k22a);
+    cudaFree(ctx->chem); cudaFree(ctx->cool); cudaFree(ctx->h2dust); cudaFree(ctx->k13a); cudaFree(ctx->k22a); cudaFree(ctx->fm_tab);
     free_cloudy(ctx->pri); free_cloudy(ctx->met);
     cudaFree(ctx->diag); cudaFreeHost(ctx->diag_host);
     for (double *p : ctx->stage) cudaFree(p);
@@ -467,7 +473,7 @@ int fill_params(GrParams &P, DeviceCtx *ctx, const chemistry_data *chem,
   P.ssh_k24 = std::pow(P.k24 / P.tbase1 / 1.0e-12, 2.0 / 3.0);
   P.ssh_k26 = std::pow(P.k26 / P.tbase1 / 1.0e-12, 2.0 / 3.0);
 
-  P.chem = ctx->chem; P.cool = ctx->cool; P.h2dust = ctx->h2dust; P.k13a = ctx->k13a; P.k22a = ctx->k22a;
+  P.chem = ctx->chem; P.cool = ctx->cool; P.h2dust = ctx->h2dust; P.k13a = ctx->k13a; P.k22a = ctx->k22a; P.fm_tab = ctx->fm_tab;
   if (cloudy_params(P.pri, ctx->pri, rates->cloudy_primordial, P.zr, P.iClHeat, P.clnew, P.log10_tcmb,
                     ctx->stream()) == GR_FAIL)
     return GR_FAIL;

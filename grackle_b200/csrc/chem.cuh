@@ -42,9 +42,9 @@ __device__ __forceinline__ void lerp_cols(const double *row, double t, double (&
 }
 
 // Rahmati+13 eq. 13/14 shielding fraction (cool1d_multi_g.F:788-792, solve_rate_cool_g.F:1518-1520)
-__device__ __forceinline__ double rahmati_f(double nratio)
+__device__ __forceinline__ double rahmati_f(const GrParams &P, double nratio)
 {
-  return 0.98 * pow_pos(1.0 + pow_pos(nratio, 1.64), -2.28) + 0.02 * pow_pos(1.0 + nratio, -0.84);
+  return 0.98 * POW_POS(1.0 + POW_POS(nratio, 1.64), -2.28) + 0.02 * POW_POS(1.0 + nratio, -0.84);
 }
 
 struct TIndex { int idx; double t1, t2, tdef; };   // idx is 1-based like the Fortran
@@ -103,7 +103,7 @@ __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool firs
         if (x > 10.0) {
           gamma2 = 0.5 * 5.0;
         } else {
-          const double ex = dexp(x);
+          const double ex = DEXP(x);
           gamma2 = 0.5 * (5.0 + ddiv(2.0 * (x * x) * ex, (ex - 1) * (ex - 1)));
         }
       } else {
@@ -118,9 +118,9 @@ __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool firs
   if (first) tgasold = th.tgas;
 
   // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211)
-  th.logtgas = (PC > 0 && lookup_follows) ? dlog(th.tgas) : 0.0;
+  th.logtgas = (PC > 0 && lookup_follows) ? DLOG(th.tgas) : 0.0;
 
-  double logtem = dlog(0.5 * (th.tgas + tgasold));
+  double logtem = DLOG(0.5 * (th.tgas + tgasold));
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
   return logtem;
@@ -167,7 +167,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     const double gael = cv(L_GAEL), h2lte = cv(L_H2LTE);
     double fudge = 1.0;
     if (P.ih2optical == 1) {
-      fudge = pow_pos(0.76 * c.d * dom / 8.e9, -0.45);
+      fudge = POW_POS(0.76 * c.d * dom / 8.e9, -0.45);
       fudge = dmin(fudge, 1.0);
     }
     const double galdl = gaHI * c.HI + gaH2 * c.H2I / 2.0 + gaHe * c.HeI / 4.0 + gaHp * c.HII + gael * c.de;
@@ -175,12 +175,12 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     edot = edot - ddiv_s((double)P.ih2co * fudge * c.H2I * h2lte, 1.0 + ddiv_s(gphdl1, galdl)) * (0.5 * dom_inv);
     if (P.iciecool == 1 && c.d * dom > 1e10) {
       const double cieco = cv(L_CIECO);
-      double tau = pow_pos((c.d / 2e16) * dom, 2.8);
+      double tau = POW_POS((c.d / 2e16) * dom, 2.8);
       tau = dmax(tau, 1.e-5);
-      double ciefudge = dmin((1.0 - dexp(-tau)) / tau, 1.0);
-      tau = pow_pos((c.d / 2.e18) * dom, 8.0);
+      double ciefudge = dmin((1.0 - DEXP(-tau)) / tau, 1.0);
+      tau = POW_POS((c.d / 2.e18) * dom, 8.0);
       tau = dmax(tau, 1.e-5);
-      ciefudge = ciefudge * dmin((1.0 - dexp(-tau)) / tau, 1.0);
+      ciefudge = ciefudge * dmin((1.0 - DEXP(-tau)) / tau, 1.0);
       edot = ciefudge * (edot - c.H2I * (c.d * cieco));
     }
   }
@@ -202,19 +202,19 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
   if (anydust) {    // gas-grain heat transfer and T_dust (:726-753)
     const double gasgr = cv(L_GASGR);
     const double gasgr_tdust = P.fgr * gasgr * P.coolunit / GRB_MASS_H;
-    th.tdust = dust_temperature(th.tgas, mynh, gasgr_tdust, P.gamma_isrfa, myisrf, P.comp2);
+    th.tdust = dust_temperature(P, th.tgas, mynh, gasgr_tdust, P.gamma_isrfa, myisrf, P.comp2);
     edot = edot - gasgr * (th.tgas - th.tdust) * th.dust2gas * th.rhoH * th.rhoH;
   }
 
   if (PC > 0) {     // UVB photo-heating with optional self-shielding (:758-913)
     double fH = 1.0, fHe = 1.0;
     if (P.iradshield >= 1 && !(P.k24 < GRB_TINY8)) {
-      const double nSSh = P.ssh_sig_hi * pow_pos(th.tgas / 1.0e4, 0.17) * P.ssh_k24;
-      fH = rahmati_f((c.HI + c.HII) * dom / nSSh);
+      const double nSSh = P.ssh_sig_hi * POW_POS(th.tgas / 1.0e4, 0.17) * P.ssh_k24;
+      fH = rahmati_f(P, (c.HI + c.HII) * dom / nSSh);
     }
     if (P.iradshield >= 2 && !(P.k26 < GRB_TINY8)) {
-      const double nSSh_he = P.ssh_sig_hei * pow_pos(th.tgas / 1.0e4, 0.17) * P.ssh_k26;
-      fHe = rahmati_f(0.25 * (c.HeI + c.HeII + c.HeIII) * dom / nSSh_he);
+      const double nSSh_he = P.ssh_sig_hei * POW_POS(th.tgas / 1.0e4, 0.17) * P.ssh_k26;
+      fHe = rahmati_f(P, 0.25 * (c.HeI + c.HeII + c.HeIII) * dom / nSSh_he);
     }
     const double ip = (double)P.ipiht;
     if (P.iradshield == 0)
@@ -243,8 +243,8 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
       geff = (th.tgas > 2.e4) ? 0.0 : P.gammaha * 0.05 * myisrf;
     } else {
       const double pe_X = myisrf * dom_inv * sqrt(th.tgas) / th.myde;
-      const double pe_eps = (4.9e-2 / (1.0 + pow_pos(pe_X / 1925.0, 0.73))) +
-                            ((3.7e-2 * pow_pos(th.tgas / 1.e4, 0.7)) / (1.0 + (pe_X / 5000.0)));
+      const double pe_eps = (4.9e-2 / (1.0 + POW_POS(pe_X / 1925.0, 0.73))) +
+                            ((3.7e-2 * POW_POS(th.tgas / 1.e4, 0.7)) / (1.0 + (pe_X / 5000.0)));
       geff = P.gammaha * pe_eps * myisrf;
     }
     edot = edot + geff * th.rhoH * dom_inv * th.dust2gas / P.fgr;
@@ -252,8 +252,8 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
 
   if ((P.idustall > 0) || (P.idustrec > 0)) {   // grain recombination cooling (:1005-1023)
     const double regr = cv(L_REGR);
-    const double grbeta = 0.74 / pow_pos(th.tgas, 0.068);
-    edot = edot - regr * pow_pos(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
+    const double grbeta = 0.74 / POW_POS(th.tgas, 0.068);
+    edot = edot - regr * POW_POS(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
   }
 
   // Compton + X-ray Compton (:1027-1041)

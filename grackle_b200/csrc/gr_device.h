@@ -110,6 +110,7 @@ struct GrParams {
   const double *h2dust;    // [ndratec][nratec]
   const double *k13a;      // raw k13, k22 columns for the H-equilibrium limiter (:606-630)
   const double *k22a;
+  const double *fm_tab;    // log/exp tables of fastmath.cuh (GRB_FM_TABLE_DOUBLES doubles)
   GrCloudyDev pri, met;
   // fields (device pointers; NULL when the physics that reads them is off)
   double *f[NFIELD];

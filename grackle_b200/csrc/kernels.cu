@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(128) k_dust_temperature(const __grid_constant_
   const double *row = P.cool + (size_t)(ti.idx - 1) * (NCOOL * 2);
   double gasgr = lerp_row(row, L_GASGR, ti.tdef);
   gasgr = gasgr * P.fgr * P.coolunit / GRB_MASS_H;
-  P.out[x] = dust_temperature(tgas, nh, gasgr, P.gamma_isrfa, myisrf, P.comp2);
+  P.out[x] = dust_temperature(P, tgas, nh, gasgr, P.gamma_isrfa, myisrf, P.comp2);
 }
 
 // ------------------------------------------------------------------------------
@@ -294,7 +294,7 @@ __device__ __forceinline__ bool subcycle_finish(const GrParams &P, Cell &c, SubS
       const double eqk221 = k22lo + (k22hi - k22lo) * eqtdef;
       const double eqk131 = k13lo + (k13hi - k13lo) * eqtdef;
       const double heq1 = ddiv(-1.0, 4.0 * eqk221) * (eqk131 - sqrt(8.0 * eqk131 * eqk221 * fd + eqk131 * eqk131));
-      const double dheq = ddiv(fabs(heq2 - heq1), dexp(eqt2) - dexp(eqt1)) * ddiv(th.tgas, th.p2d) * edot;
+      const double dheq = ddiv(fabs(heq2 - heq1), DEXP(eqt2) - DEXP(eqt1)) * ddiv(th.tgas, th.p2d) * edot;
       const double heq = ddiv(-1.0, 4.0 * RK(k22)) * (RK(k13) - sqrt(8.0 * RK(k13) * RK(k22) * fd + RK(k13) * RK(k13)));
       dtit = dmin(dtit, ddiv(0.1 * heq, dheq));
     }
@@ -570,13 +570,16 @@ __host__ __device__ inline void lean_flags(GrParams &P)
 template <int PC, bool LEAN>
 __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P0)
 {
-  if (LEAN) {
-    GrParams P = P0;
-    lean_flags(P);
-    solve_cells<PC>(P);
-  } else {
-    solve_cells<PC>(P0);
-  }
+  // the 2.5 KB log/exp table goes to shared memory behind the slot rows; the by-value copy of
+  // the parameters is what lets the compiler fold the LEAN switches and the table pointer
+  extern __shared__ double slot_rows[];
+  double *const fm = slot_rows + (size_t)GRB_SOLVE_THREADS * GRB_SLOT_STRIDE;
+  for (int i = threadIdx.x; i < GRB_FM_TABLE_DOUBLES; i += GRB_SOLVE_THREADS) fm[i] = P0.fm_tab[i];
+  __syncthreads();
+  GrParams P = P0;
+  P.fm_tab = fm;
+  if (LEAN) lean_flags(P);
+  solve_cells<PC>(P);
 }
 
 // ------------------------------------------------------------------------------
@@ -601,7 +604,7 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double *sink, int iters, doub
 // ------------------------------------------------------------------------------
 // host-callable launchers (declared in gr_launch.h)
 // ------------------------------------------------------------------------------
-#define GRB_SOLVE_SMEM ((size_t)GRB_SLOT_STRIDE * GRB_SOLVE_THREADS * sizeof(double))
+#define GRB_SOLVE_SMEM (((size_t)GRB_SLOT_STRIDE * GRB_SOLVE_THREADS + GRB_FM_TABLE_DOUBLES) * sizeof(double))
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 }  // namespace grb

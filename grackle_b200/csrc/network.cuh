@@ -53,12 +53,12 @@ __device__ inline double k13_martin(const GrParams &P, const Cell &c, const Ther
   double k13 = GRB_TINY8;
   if (th.tgas >= 500.0 && th.tgas < 1.0e6) {
 #define DD(n) (slots[SLA_DD + (n)])
-    double cid = DD(0) - ddiv(DD(1), 1.0 + pow_pos(ddiv(nh, DD(4)), DD(6))) + DD(2) -
-                 ddiv(DD(3), 1.0 + pow_pos(ddiv(nh, DD(5)), DD(6)));
-    cid = dmax(dexp10(cid), GRB_TINY8);
-    double dtn = DD(7) - ddiv(DD(8), 1.0 + pow_pos(ddiv(nh, DD(11)), DD(13))) + DD(9) -
-                 ddiv(DD(10), 1.0 + pow_pos(ddiv(nh, DD(12)), DD(13)));
-    dtn = dmax(dexp10(dtn), GRB_TINY8);
+    double cid = DD(0) - ddiv(DD(1), 1.0 + POW_POS(ddiv(nh, DD(4)), DD(6))) + DD(2) -
+                 ddiv(DD(3), 1.0 + POW_POS(ddiv(nh, DD(5)), DD(6)));
+    cid = dmax(DEXP10(cid), GRB_TINY8);
+    double dtn = DD(7) - ddiv(DD(8), 1.0 + POW_POS(ddiv(nh, DD(11)), DD(13))) + DD(9) -
+                 ddiv(DD(10), 1.0 + POW_POS(ddiv(nh, DD(12)), DD(13)));
+    dtn = dmax(DEXP10(dtn), GRB_TINY8);
     k13 = dtn + cid;
 #undef DD
   }
@@ -81,7 +81,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
     if (th.tdust > P.dtemend) {
       RS(h2dust) = GRB_TINY8;
     } else {
-      double dl = dlog(th.tdust);
+      double dl = DLOG(th.tdust);
       dl = dmax(dl, P.d_logtem0);
       dl = dmin(dl, P.d_logtem9);
       const long long di = imin(P.ndratec - 1, imax(1, (long long)((dl - P.d_logtem0) / P.d_dlogtem) + 1));
@@ -124,12 +124,12 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
       tuse = dmin(tuse, 8e3);
       double nuse = c.d * dom / th.mmw;
       nuse = dmin(nuse, 1e7);
-      const double aWG = (0.8711 * dlog10(tuse) - 1.928) * dexp(-0.2856 * dlog10(nuse)) +
-                         (-0.9639 * dlog10(tuse) + 3.892);
+      const double aWG = (0.8711 * DLOG10(tuse) - 1.928) * DEXP(-0.2856 * DLOG10(nuse)) +
+                         (-0.9639 * DLOG10(tuse) + 3.892);
       const double x = 2.0e-15 * N_H2;
       const double b_doppler = 1e-5 * sqrt(2.0 * GRB_KBOLTZ * th.tgas / GRB_MASS_H);
-      double f_shield = 0.965 / pow_pos(1.0 + x / b_doppler, aWG) +
-                        0.035 * dexp(-8.5e-4 * sqrt(1.0 + x)) / sqrt(1.0 + x);
+      double f_shield = 0.965 / POW_POS(1.0 + x / b_doppler, aWG) +
+                        0.035 * DEXP(-8.5e-4 * sqrt(1.0 + x)) / sqrt(1.0 + x);
       f_shield = dmin(f_shield, 1.0);
       RS(k31s) = f_shield * RS(k31s);
     }
@@ -137,16 +137,16 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
   }
 
   if (P.iradshield > 0) {   // UVB self-shielding (:1492-1676)
-    const double tfac = pow_pos(th.tgas / 1.0e4, 0.17);
+    const double tfac = POW_POS(th.tgas / 1.0e4, 0.17);
     double nratio = (c.HI + c.HII);
     if (PC > 1) {
       nratio = nratio + c.HM + c.H2I + c.H2II;
       if (PC > 2) nratio = nratio + 0.5 * (c.DI + c.DII) + 2.0 * c.HDI / 3.0;
     }
     nratio = nratio * dom / (P.ssh_sig_hi * tfac * P.ssh_k24);
-    const double fH = rahmati_f(nratio);
+    const double fH = rahmati_f(P, nratio);
     nratio = 0.25 * (c.HeI + c.HeII + c.HeIII) * dom / (P.ssh_sig_hei * tfac * P.ssh_k26);
-    const double fHe = rahmati_f(nratio);
+    const double fHe = rahmati_f(P, nratio);
     RS(k24s) = (P.k24 < GRB_TINY8) ? 0.0 : RS(k24s) * fH;
     RS(k29s) = (P.k29 < GRB_TINY8) ? 0.0 : RS(k29s) * fH;
     if (P.iradshield == 1) {

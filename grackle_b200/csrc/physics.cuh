@@ -45,8 +45,14 @@ __device__ __forceinline__ double ld(const double *p) { return __ldg(p); }
 __device__ __forceinline__ double sq(double x) { return x * x; }
 // x**y for x >= 0 as exp(y ln x): every real power on this path has a non-negative base.
 // |y ln x| < 1e2 here, so the result is within ~1e-14 relative of the correctly rounded
-// power (the tolerances are 1e-9 / 1e-6) at well under half the instructions of pow().
-__device__ __forceinline__ double pow_pos(double x, double y) { return dexp(y * dlog(x)); }
+// power (the tolerances are 1e-9 / 1e-6) at a fraction of the instructions of pow().
+// The elementary functions are the table-driven ones of fastmath.cuh; every caller has the
+// kernel parameters `P` in scope, which carry the table pointer.
+#define DLOG(x) dlog((x), P.fm_tab)
+#define DLOG10(x) dlog10((x), P.fm_tab)
+#define DEXP(x) dexp((x), P.fm_tab)
+#define DEXP10(x) dexp10((x), P.fm_tab)
+#define POW_POS(x, y) dpow_pos((x), (y), P.fm_tab)
 __device__ __forceinline__ double pow4(double x) { const double x2 = x * x; return x2 * x2; }
 
 // 1-based clamped index on a uniform axis (interpolators_g.F:28-29 and friends)
@@ -132,7 +138,7 @@ __device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCl
                                                    int iZscale)
 {
   const double log10tem = logtem * GRB_INV_LN10;
-  const double log_n_h = dlog10(rhoH * P.dom);
+  const double log_n_h = DLOG10(rhoH * P.dom);
   int i1 = (int)((log_n_h - c.par0[0]) * c.inv_dpar[0]) + 1;
   i1 = min(c.fdim[0] - 1, max(1, i1));
   int i2 = (int)((log10tem - c.par0[1]) * c.inv_dpar[1]) + 1;
@@ -145,11 +151,11 @@ __device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCl
   double m0 = 0.0, m1 = 0.0;
   if (floor_on) { m0 = ld(c.cmb + i1 - 1); m1 = ld(c.cmb + i1); }
   const double c0 = w2 * (v01.x - v00.x) + v00.x, c1 = w2 * (v11.x - v10.x) + v10.x;
-  double edot_met = -dexp10(w1 * (c1 - c0) + c0);
-  if (floor_on) edot_met = edot_met + dexp10(w1 * (m1 - m0) + m0);
+  double edot_met = -DEXP10(w1 * (c1 - c0) + c0);
+  if (floor_on) edot_met = edot_met + DEXP10(w1 * (m1 - m0) + m0);
   if (c.get_heat == 1) {
     const double h0 = w2 * (v01.y - v00.y) + v00.y, h1 = w2 * (v11.y - v10.y) + v10.y;
-    edot_met = edot_met + dexp10(w1 * (h1 - h0) + h0);
+    edot_met = edot_met + DEXP10(w1 * (h1 - h0) + h0);
   }
   if (iZscale == 1) edot_met = edot_met * metallicity;
   return edot_met * rhoH * rhoH;
@@ -161,12 +167,12 @@ __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, do
   if (c.fast == 1) return cloudy_edot_fast(P, c, rhoH, metallicity, logtem, icmbTfloor, iZscale);
   const double log10_tCMB = P.log10_tcmb;
   const double log10tem = logtem * GRB_INV_LN10;
-  const double log_n_h = dlog10(rhoH * P.dom);
-  double edot_met = -dexp10(cloudy_lookup(c, c.cooling, log_n_h, log10tem));
+  const double log_n_h = DLOG10(rhoH * P.dom);
+  double edot_met = -DEXP10(cloudy_lookup(c, c.cooling, log_n_h, log10tem));
   if (icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
-    edot_met = edot_met + dexp10(cloudy_lookup(c, c.cooling, log_n_h, log10_tCMB));
+    edot_met = edot_met + DEXP10(cloudy_lookup(c, c.cooling, log_n_h, log10_tCMB));
   if (c.get_heat == 1)
-    edot_met = edot_met + dexp10(cloudy_lookup(c, c.heating, log_n_h, log10tem));
+    edot_met = edot_met + DEXP10(cloudy_lookup(c, c.heating, log_n_h, log10tem));
   if (iZscale == 1) edot_met = edot_met * metallicity;
   return edot_met * rhoH * rhoH;
 }
@@ -179,17 +185,17 @@ __device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c
   const double log10_tCMB = P.log10_tcmb;        // see oracle note on the unassigned upstream local
   const double log10tem = logtem * GRB_INV_LN10;
   double log_n_h = 0.0, log_Z = 0.0;
-  if (c.rank > 1) log_n_h = dlog10(rhoH * P.dom);
-  if (c.rank > 2) log_Z = dlog10(metallicity);
+  if (c.rank > 1) log_n_h = DLOG10(rhoH * P.dom);
+  if (c.rank > 2) log_Z = DLOG10(metallicity);
   auto look = [&](const double *data, double lt) {
     if (c.rank == 1) return interp1(c, data, lt);
     if (c.rank == 2) return interp2(c, data, log_n_h, lt);
     return interp3(c, data, log_n_h, log_Z, lt);
   };
-  double edot_met = -dexp10(look(c.cooling, log10tem));
+  double edot_met = -DEXP10(look(c.cooling, log10tem));
   if (P.icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
-    edot_met = edot_met + dexp10(look(c.cooling, log10_tCMB));
-  if (P.iClHeat == 1) edot_met = edot_met + dexp10(look(c.heating, log10tem));
+    edot_met = edot_met + DEXP10(look(c.cooling, log10_tCMB));
+  if (P.iClHeat == 1) edot_met = edot_met + DEXP10(look(c.heating, log10tem));
   return edot_met * rhoH * d;
 }
 
@@ -199,12 +205,12 @@ __device__ inline void temperature_table(const GrParams &P, double d, double e, 
 {
   const GrCloudyDev &c = P.pri;
   const double inv_log10 = GRB_INV_LN10;
-  const double log_n_h = dlog10(rhoH * P.dom);
+  const double log_n_h = DLOG10(rhoH * P.dom);
   double munew = 1.0, muold = 1.0;
   for (int ti = 1; ti <= 20; ti++) {
     muold = munew;
     tgas = dmax((P.gamma - 1.0) * e * munew * P.utem, P.temstart);
-    const double log10tem = dlog(tgas) * inv_log10;
+    const double log10tem = DLOG(tgas) * inv_log10;
     munew = cloudy_lookup(c, c.mmw, log_n_h, log10tem);
     munew = 0.5 * (munew + muold);
     tgas = tgas * munew / muold;
@@ -235,8 +241,8 @@ __device__ __forceinline__ double gr_balance(double td, double tgas, double kgr,
   return gamma_isrf + (4.0 * GRB_SIGMA_SB) * kgr * (trad4 - pow4(td)) + (gasgr * nh * (tgas - td));
 }
 
-__device__ inline double dust_temperature(double tgas, double nh, double gasgr, double gamma_isrfa,
-                                          double isrf, double trad_in)
+__device__ inline double dust_temperature(const GrParams &P, double tgas, double nh, double gasgr,
+                                          double gamma_isrfa, double isrf, double trad_in)
 {
   const double t_subl = 1.5e3, radf = 4.0 * GRB_SIGMA_SB, kgr1 = 4.0e-4;
   const double trad = dmax(1.0, trad_in);
@@ -249,7 +255,7 @@ __device__ inline double dust_temperature(double tgas, double nh, double gasgr, 
   } else if (tgas > t_subl) {
     newton = false;
   } else {
-    td = dmax(trad, pow_pos(gamma_isrf / radf / kgr1, 0.17));
+    td = dmax(trad, POW_POS(gamma_isrf / radf / kgr1, 0.17));
   }
   for (int it = 1; it <= 50 && newton; it++) {
     const double tdp = dmax(1.e-3, ((1.0 + pert) * td));

@@ -13,7 +13,7 @@ __device__ double rel(double a, double b)
   return fabs(a - b) / fmax(fabs(b), 1e-300);
 }
 
-__global__ void k_check(double *worst, unsigned long long *bad)
+__global__ void k_check(double *worst, unsigned long long *bad, const double *tab)
 {
   const int ea = (int)blockIdx.x - 300;            // exponent of a: 10^-300 .. 10^300
   const int eb = (int)threadIdx.x * 2 - 300;       // exponent of b
@@ -47,20 +47,35 @@ __global__ void k_check(double *worst, unsigned long long *bad)
     const double f = rel(grb::dexp10(y), exp10(y));
     if (f > 1e-15) atomicAdd(bad + 4, 1ULL);
     atomicMax((unsigned long long *)worst + 4, (unsigned long long)__double_as_longlong(f));
+    // table-driven versions (the ones the kernels call)
+    const double e6 = rel(grb::dexp(x, tab), exp(x));
+    if (e6 > 1e-15) atomicAdd(bad + 6, 1ULL);
+    atomicMax((unsigned long long *)worst + 6, (unsigned long long)__double_as_longlong(e6));
+    const double e7 = rel(grb::dexp10(y, tab), exp10(y));
+    if (e7 > 1e-15) atomicAdd(bad + 7, 1ULL);
+    atomicMax((unsigned long long *)worst + 7, (unsigned long long)__double_as_longlong(e7));
+  }
+  {
+    const double e = fabs(grb::dlog(a, tab) - log(a)) / fmax(fabs(log(a)), 1.0);
+    if (e > 1e-15) atomicAdd(bad + 5, 1ULL);
+    atomicMax((unsigned long long *)worst + 5, (unsigned long long)__double_as_longlong(e));
   }
 }
 
 int main()
 {
   double *worst; unsigned long long *bad;
-  cudaMallocManaged(&worst, 5 * sizeof(double));
-  cudaMallocManaged(&bad, 5 * sizeof(unsigned long long));
-  for (int i = 0; i < 5; i++) { worst[i] = 0; bad[i] = 0; }
-  k_check<<<601, 301>>>(worst, bad);
+  double *tab;
+  cudaMallocManaged(&worst, 8 * sizeof(double));
+  cudaMallocManaged(&bad, 8 * sizeof(unsigned long long));
+  cudaMallocManaged(&tab, GRB_FM_TABLE_DOUBLES * sizeof(double));
+  grb::fm_fill_tables(tab);
+  for (int i = 0; i < 8; i++) { worst[i] = 0; bad[i] = 0; }
+  k_check<<<601, 301>>>(worst, bad, tab);
   if (cudaDeviceSynchronize() != cudaSuccess) { std::printf("cuda error\n"); return 2; }
-  const char *names[5] = {"div", "rcp", "log", "exp", "exp10"};
+  const char *names[8] = {"div", "rcp", "log", "exp", "exp10", "tlog", "texp", "texp10"};
   int rc = 0;
-  for (int i = 0; i < 5; i++) {
+  for (int i = 0; i < 8; i++) {
     std::printf("%s %.3e %llu\n", names[i], worst[i], bad[i]);
     if (bad[i]) rc = 1;
   }

@@ -28,9 +28,34 @@ static void sweep(const char *name, F f, R ref, double lo, double hi, bool logsp
   std::printf("%s %.3f %.3e %.17g\n", name, worst_ulp, worst_rel, at);
 }
 
+template <class F, class R>
+static void sweep_abs(const char *name, F f, R ref, double lo, double hi, bool logspace, int n)
+{
+  std::mt19937_64 g(4321);
+  std::uniform_real_distribution<double> u(0.0, 1.0);
+  double worst = 0, at = 0;
+  for (int i = 0; i < n; i++) {
+    double x = logspace ? std::exp(std::log(lo) + (std::log(hi) - std::log(lo)) * u(g)) : lo + (hi - lo) * u(g);
+    const long double want = ref((long double)x);
+    const double err = (double)(fabsl((long double)f(x) - want) / fmaxl(1.0L, fabsl(want)));
+    if (err > worst) { worst = err; at = x; }
+  }
+  std::printf("%s %.3e %.17g\n", name, worst, at);
+}
+
 int main()
 {
   const int N = 2000000;
+  static double tab[GRB_FM_TABLE_DOUBLES];
+  grb::fm_fill_tables(tab);
+  // table-driven versions: error relative to max(1, |result|) for log, relative for exp
+  sweep_abs("tlog_wide", [&](double x) { return grb::dlog(x, tab); }, [](long double x) { return logl(x); }, 1e-300, 1e300, true, N);
+  sweep_abs("tlog_near1", [&](double x) { return grb::dlog(x, tab); }, [](long double x) { return logl(x); }, 0.25, 4.0, false, N);
+  sweep("tlog_far", [&](double x) { return grb::dlog(x, tab); }, [](long double x) { return logl(x); }, 3.0, 1e12, true, N);
+  sweep("texp", [&](double x) { return grb::dexp(x, tab); }, [](long double x) { return expl(x); }, -700.0, 700.0, false, N);
+  sweep("texp_small", [&](double x) { return grb::dexp(x, tab); }, [](long double x) { return expl(x); }, -2.0, 2.0, false, N);
+  sweep("texp10", [&](double x) { return grb::dexp10(x, tab); }, [](long double x) { return powl(10.0L, x); }, -300.0, 300.0, false, N);
+  sweep("tpow", [&](double x) { return grb::dpow_pos(x, 1.37, tab); }, [](long double x) { return powl(x, 1.37L); }, 1e-12, 1e12, true, N);
   sweep("log_wide", [](double x) { return grb::dlog(x); }, [](long double x) { return logl(x); }, 1e-300, 1e300, true, N);
   sweep("log_near1", [](double x) { return grb::dlog(x); }, [](long double x) { return logl(x); }, 0.5, 2.0, false, N);
   sweep("log10", [](double x) { return grb::dlog10(x); }, [](long double x) { return log10l(x); }, 1e-12, 1e12, true, N);

@@ -19,5 +19,10 @@ def test_fastmath_matches_libm(tmp_path):
               "exp10": 2.0, "exp10_small": 2.0, "rcp": 1.0, "div": 1.0}
     for name, lim in limits.items():
         assert float(rows[name][0]) <= lim, (name, rows[name])
+    # table-driven versions (the ones the kernels call): log in absolute terms near x = 1
+    assert float(rows["tlog_wide"][0]) <= 4e-16 and float(rows["tlog_near1"][0]) <= 4e-16
+    for name in ("tlog_far", "texp", "texp_small", "texp10"):
+        assert float(rows[name][0]) <= 2.0, (name, rows[name])
+    assert float(rows["tpow"][1]) <= 3e-14, rows["tpow"]
     # x**y = exp(y ln x) amplifies the log error by |y ln x| (here <= 38): relative bound instead
     assert float(rows["pow"][1]) <= 2e-14, rows["pow"]

@@ -178,7 +178,8 @@ def test_fastmath_on_device():
     assert out.returncode == 0, out.stdout + out.stderr
     rows = {ln.split()[0]: ln.split()[1:] for ln in out.stdout.strip().splitlines()}
     assert float(rows["div"][0]) <= 2.3e-16 and float(rows["rcp"][0]) <= 2.3e-16
-    assert float(rows["log"][0]) <= 1e-15 and float(rows["exp"][0]) <= 1e-15 and float(rows["exp10"][0]) <= 1e-15
+    for name in ("log", "exp", "exp10", "tlog", "texp", "texp10"):
+        assert float(rows[name][0]) <= 1e-15, (name, rows[name])
 
 
 def test_conservation_after_solve(pairs, synth_table):
