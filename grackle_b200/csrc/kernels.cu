@@ -176,9 +176,14 @@ __global__ void __launch_bounds__(256) k_temperature_table(const __grid_constant
 }
 
 // cool_multi_time_g.F: one cool_rate evaluation, t_cool = max(p/(gamma-1), tiny)/edot
-template <int PC>
-__global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ GrParams P)
+__host__ __device__ inline void lean_flags(GrParams &P);
+
+// LEAN: the optional physics modules folded to "off" at compile time, as for k_solve (below)
+template <int PC, bool LEAN>
+__global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ GrParams P0)
 {
+  GrParams P = P0;
+  if (LEAN) lean_flags(P);
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= P.nactive) return;
   int i, j, k;
@@ -643,7 +648,10 @@ void grb_launch_temperature_table(const GrParams &P, cudaStream_t st)
 void grb_launch_cooling_time(const GrParams &P, cudaStream_t st)
 {
   const unsigned nb = blocks_for(P.nactive, 128);
-#define CALL(PCV) k_cooling_time<PCV><<<nb, 128, 0, st>>>(P);
+  const bool lean = (grb_solve_variant == 0) && grb_solve_is_lean(P);
+#define CALL(PCV)                                             \
+  if (lean) k_cooling_time<PCV, true><<<nb, 128, 0, st>>>(P); \
+  else k_cooling_time<PCV, false><<<nb, 128, 0, st>>>(P);
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
 }
