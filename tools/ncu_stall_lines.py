@@ -26,6 +26,7 @@ by = collections.defaultdict(collections.Counter); byop = collections.defaultdic
 inst_line = collections.Counter(); tot = collections.Counter()
 for r in rows[2:]:
     if len(r) <= ii: continue
+    if r[ia] == "Address": break          # a second kernel's table follows: only the first is analysed
     a = int(r[ia], 16) if r[ia].startswith("0x") else int(r[ia])
     if base is None: base = a
     key, txt = addr2.get(a - base, (("?", 0), "?"))
