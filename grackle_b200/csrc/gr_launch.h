@@ -17,7 +17,7 @@ void grb_launch_temperature_table(const GrParams &P, cudaStream_t st);
 void grb_launch_cooling_time(const GrParams &P, cudaStream_t st);
 void grb_launch_dust_temperature(const GrParams &P, cudaStream_t st);
 void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st);
-bool grb_solve_is_lean(const GrParams &P);
+int grb_solve_variant_for(const GrParams &P);   // 0 general, 1 lean, 2 lean + H2-on-dust + UVB self-shielding
 extern int grb_solve_variant;       // 0 = choose per call, 1 = always the general instantiation
 int grb_solve_max_blocks_per_sm(int pc);
 double grb_launch_fp64_peak(double *sink, int blocks, int iters, cudaStream_t st);

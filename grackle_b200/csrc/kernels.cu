@@ -176,14 +176,15 @@ __global__ void __launch_bounds__(256) k_temperature_table(const __grid_constant
 }
 
 // cool_multi_time_g.F: one cool_rate evaluation, t_cool = max(p/(gamma-1), tiny)/edot
-__host__ __device__ inline void lean_flags(GrParams &P);
+template <int VAR>
+__host__ __device__ inline void variant_flags(GrParams &P);
 
-// LEAN: the optional physics modules folded to "off" at compile time, as for k_solve (below)
-template <int PC, bool LEAN>
+// VAR: optional physics modules folded to "off" at compile time, as for k_solve (below)
+template <int PC, int VAR>
 __global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ GrParams P0)
 {
   GrParams P = P0;
-  if (LEAN) lean_flags(P);
+  variant_flags<VAR>(P);
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= P.nactive) return;
   int i, j, k;
@@ -556,34 +557,43 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
   }
 }
 
-// Two instantiations per network.  The executed path of a subcycle is far larger than the
+// Three instantiations per network.  The executed path of a subcycle is far larger than the
 // SM's instruction cache, so what is NOT executed matters too: with every optional physics
 // module compiled in, the hot instructions of the common configuration are scattered over
-// 260 KB of SASS.  LEAN folds the switches of the modules below to "off" at compile time
+// 260 KB of SASS.  A variant folds the switches of modules it omits to "off" at compile time
 // (a by-value copy of the parameters whose flags are overwritten with constants; the
-// compiler propagates them and drops the dead code: 16.4k -> 8.0k instructions, +32 %
-// cells/s at config C4).  grb_solve_is_lean() is the host-side test for that case; any
-// other parameter set runs the general instantiation.
-__host__ __device__ inline void lean_flags(GrParams &P)
+// compiler propagates them and drops the dead code: 16.4k -> 5.6k instructions, +32 %
+// cells/s at config C4):
+//   VAR_GENERAL      everything, all switches read at run time
+//   VAR_LEAN         network + metal cooling + UV background (configs C1, C2, C4)
+//   VAR_DUST_SHIELD  VAR_LEAN + H2 formation on dust (h2_on_dust, no dust field) + UVB
+//                    self-shielding, any method (config C3)
+// grb_solve_variant_for() is the host-side choice; anything else runs VAR_GENERAL.
+enum { VAR_GENERAL = 0, VAR_LEAN = 1, VAR_DUST_SHIELD = 2 };
+
+template <int VAR>
+__host__ __device__ inline void variant_flags(GrParams &P)
 {
-  P.idust = 0; P.idustall = 0; P.idustfield = 0; P.idustrec = 0; P.igammah = 0; P.ih2optical = 0;
-  P.iciecool = 0; P.ithreebody = 0; P.iH2shield = 0; P.iradshield = 0; P.iradtrans = 0; P.iradcoupled = 0;
+  if (VAR == VAR_GENERAL) return;
+  P.idustall = 0; P.idustfield = 0; P.idustrec = 0; P.igammah = 0; P.ih2optical = 0;
+  P.iciecool = 0; P.ithreebody = 0; P.iH2shield = 0; P.iradtrans = 0; P.iradcoupled = 0;
   P.iVheat = 0; P.iMheat = 0; P.iisrffield = 0; P.iH2shieldcustom = 0; P.clnew = 1;
   P.met.fast = 1; P.pri.fast = 1;
+  if (VAR == VAR_LEAN) { P.idust = 0; P.iradshield = 0; }
 }
 
-template <int PC, bool LEAN>
+template <int PC, int VAR>
 __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P0)
 {
   // the 2.5 KB log/exp table goes to shared memory behind the slot rows; the by-value copy of
-  // the parameters is what lets the compiler fold the LEAN switches and the table pointer
+  // the parameters is what lets the compiler fold the variant's switches and the table pointer
   extern __shared__ double slot_rows[];
   double *const fm = slot_rows + (size_t)GRB_SOLVE_THREADS * GRB_SLOT_STRIDE;
   for (int i = threadIdx.x; i < GRB_FM_TABLE_DOUBLES; i += GRB_SOLVE_THREADS) fm[i] = P0.fm_tab[i];
   __syncthreads();
   GrParams P = P0;
   P.fm_tab = fm;
-  if (LEAN) lean_flags(P);
+  variant_flags<VAR>(P);
   solve_cells<PC>(P);
 }
 
@@ -648,10 +658,11 @@ void grb_launch_temperature_table(const GrParams &P, cudaStream_t st)
 void grb_launch_cooling_time(const GrParams &P, cudaStream_t st)
 {
   const unsigned nb = blocks_for(P.nactive, 128);
-  const bool lean = (grb_solve_variant == 0) && grb_solve_is_lean(P);
-#define CALL(PCV)                                             \
-  if (lean) k_cooling_time<PCV, true><<<nb, 128, 0, st>>>(P); \
-  else k_cooling_time<PCV, false><<<nb, 128, 0, st>>>(P);
+  const int var = grb_solve_variant_for(P);
+#define CALL(PCV)                                                                      \
+  if (var == VAR_LEAN) k_cooling_time<PCV, VAR_LEAN><<<nb, 128, 0, st>>>(P);           \
+  else if (var == VAR_DUST_SHIELD) k_cooling_time<PCV, VAR_DUST_SHIELD><<<nb, 128, 0, st>>>(P); \
+  else k_cooling_time<PCV, VAR_GENERAL><<<nb, 128, 0, st>>>(P);
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
 }
@@ -666,40 +677,46 @@ void grb_launch_dust_temperature(const GrParams &P, cudaStream_t st)
 
 int grb_solve_variant = 0;
 
-// true when the parameter set leaves every module off that the LEAN instantiation folds away
-bool grb_solve_is_lean(const GrParams &P)
+// which instantiation serves this parameter set (VAR_* above)
+int grb_solve_variant_for(const GrParams &P)
 {
+  if (grb_solve_variant != 0) return VAR_GENERAL;
   // "off" is <= 0 for every switch (unset options stay at -1, e.g. dust_recombination_cooling)
-  const bool off = P.idust <= 0 && P.idustall <= 0 && P.idustfield <= 0 && P.idustrec <= 0 && P.igammah <= 0 &&
-                   P.ih2optical <= 0 && P.iciecool <= 0 && P.iH2shield <= 0 && P.iradshield <= 0 &&
+  const bool off = P.idustall <= 0 && P.idustfield <= 0 && P.idustrec <= 0 && P.igammah <= 0 &&
+                   P.ih2optical <= 0 && P.iciecool <= 0 && P.iH2shield <= 0 &&
                    P.iradtrans <= 0 && P.iVheat <= 0 && P.iMheat <= 0 && P.iisrffield <= 0 && P.iH2shieldcustom <= 0;
-  return off && (P.ispecies < 2 || P.ithreebody == 0) && (P.imcool == 0 || (P.clnew == 1 && P.met.fast == 1)) &&
-         (P.ispecies > 0 || P.pri.fast == 1);
+  const bool ok = off && (P.ispecies < 2 || P.ithreebody == 0) && (P.imcool == 0 || (P.clnew == 1 && P.met.fast == 1)) &&
+                  (P.ispecies > 0 || P.pri.fast == 1);
+  if (!ok) return VAR_GENERAL;
+  if (P.idust <= 0 && P.iradshield <= 0) return VAR_LEAN;
+  return (P.ispecies > 0) ? VAR_DUST_SHIELD : VAR_GENERAL;
 }
 
 // persistent launch: `blocks` CTAs of GRB_SOLVE_THREADS threads (host picks a multiple of
 // the SM count); P.work_counter must be zero
 void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
 {
-  const bool lean = (grb_solve_variant == 0) && grb_solve_is_lean(P);
-#define CALL(PCV)                                                                                           \
-  if (lean) {                                                                                               \
-    cudaFuncSetAttribute(k_solve<PCV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);  \
-    k_solve<PCV, true><<<blocks, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM, st>>>(P);                               \
-  } else {                                                                                                  \
-    cudaFuncSetAttribute(k_solve<PCV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM); \
-    k_solve<PCV, false><<<blocks, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM, st>>>(P);                              \
+  const int var = grb_solve_variant_for(P);
+#define LAUNCH(PCV, V)                                                                                   \
+  {                                                                                                      \
+    cudaFuncSetAttribute(k_solve<PCV, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);  \
+    k_solve<PCV, V><<<blocks, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM, st>>>(P);                               \
   }
+#define CALL(PCV)                                                   \
+  if (var == VAR_LEAN) LAUNCH(PCV, VAR_LEAN)                        \
+  else if (var == VAR_DUST_SHIELD) LAUNCH(PCV, VAR_DUST_SHIELD)     \
+  else LAUNCH(PCV, VAR_GENERAL)
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
+#undef LAUNCH
 }
 
 int grb_solve_max_blocks_per_sm(int pc)
 {
   int n = 0;
 #define CALL(PCV)                                                                                           \
-  cudaFuncSetAttribute(k_solve<PCV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);   \
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV, false>, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM);
+  cudaFuncSetAttribute(k_solve<PCV, VAR_GENERAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);   \
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV, VAR_GENERAL>, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM);
   DISPATCH_PC(pc, CALL)
 #undef CALL
   return n;

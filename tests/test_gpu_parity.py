@@ -144,10 +144,11 @@ def test_results_independent_of_lane_assignment(pairs, synth_table):
         assert np.array_equal(f1[k][perm], f3[k]), k
 
 
-@pytest.mark.parametrize("name", ["C1", "C2", "C4"])
+@pytest.mark.parametrize("name", ["C1", "C2", "C3", "C4"])
 def test_compact_and_general_solve_kernels_agree(pairs, synth_table, product_lib, name):
     """configurations with the optional modules off run a compact instantiation of the solve
-    kernel (kernels.cu: LEAN); forcing the general instantiation must give the same cells"""
+    kernel (kernels.cu: VAR_LEAN for C1/C2/C4, VAR_DUST_SHIELD for C3); forcing the general
+    instantiation must give the same cells"""
     cp, co, dt = pairs[name]
     n = 4096
     fields, dt = parity.config_inputs(name, synth_table, n, "B", co)
