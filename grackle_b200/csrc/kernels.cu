@@ -44,7 +44,7 @@ __device__ __forceinline__ void load_cell(const GrParams &P, size_t x, Cell &c, 
   const bool sc = (P.iexpand == 1);
   // solve multiplies by aye**(-3) (solve_rate_cool_g.F:353); cooling time divides by aye**3
   // (cool_multi_time_g.F:163): keep each spelling so roundings match
-#define LDF(id) (sc ? (SCALE_DIV ? P.f[id][x] / P.a3 : P.f[id][x] * s) : P.f[id][x])
+#define LDF(id) (sc ? (SCALE_DIV ? ddiv(P.f[id][x], P.a3) : P.f[id][x] * s) : P.f[id][x])
   c.d = LDF(F_D);
   c.e = P.f[F_E][x];
   c.metal = (P.imetal == 1) ? LDF(F_METAL) : 0.0;
@@ -178,25 +178,6 @@ __global__ void __launch_bounds__(256) k_temperature_table(const __grid_constant
 // cool_multi_time_g.F: one cool_rate evaluation, t_cool = max(p/(gamma-1), tiny)/edot
 template <int VAR>
 __host__ __device__ inline void variant_flags(GrParams &P);
-
-// VAR: optional physics modules folded to "off" at compile time, as for k_solve (below)
-template <int PC, int VAR>
-__global__ void __launch_bounds__(128) k_cooling_time(const __grid_constant__ GrParams P0)
-{
-  GrParams P = P0;
-  variant_flags<VAR>(P);
-  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= P.nactive) return;
-  int i, j, k;
-  const size_t x = cell_index(P, t, i, j, k);
-  Cell c;
-  load_cell<PC, true>(P, x, c, false);
-  Thermo th;
-  double tgasold = 0.0;
-  cool_rate<PC>(P, c, true, tgasold, th, false);
-  const double energy = dmax(th.p2d / (P.gamma - 1.0), GRB_TINY);
-  P.out[x] = energy / th.edot;
-}
 
 // calc_tdust_3d_g.F: gas temperature comes in through P.f[F_VHEAT] (scratch slot)
 template <int PC>
@@ -408,7 +389,7 @@ __device__ __forceinline__ bool group_any(int bar_id, bool pred)
 // All loads of a pass are independent of each other.
 // (explicit load batches over passes and a group barrier only every 2nd/4th subcycle were
 // measured slower than letting the compiler schedule this loop.)
-template <int G, int NCOLS, int ROWB>
+template <int G, int NCOLS, int ROWB, int STRIDE = GRB_SLOT_STRIDE>
 __device__ __forceinline__ void coop_fetch(const double *table, int my_off, double my_t, double *dst0)
 {
   static_assert(G == 2 || G == 4 || G == 8 || G == 16, "lanes per cell");
@@ -418,7 +399,7 @@ __device__ __forceinline__ void coop_fetch(const double *table, int my_off, doub
   constexpr int CPP = 32 / G;                 // cells per pass
   constexpr int PER = (NCOLS + G - 1) / G;    // columns per lane
   const char *src = reinterpret_cast<const char *>(table) + 16 * g;
-  double *dst = dst0 + sub * GRB_SLOT_STRIDE + g;
+  double *dst = dst0 + sub * STRIDE + g;
 #pragma unroll
   for (int pass = 0; pass < G; pass++) {
     const int cell = pass * CPP + sub;
@@ -428,9 +409,58 @@ __device__ __forceinline__ void coop_fetch(const double *table, int my_off, doub
     for (int k = 0; k < PER; k++) {
       if ((k + 1) * G <= NCOLS || g + k * G < NCOLS) {
         const double2 p = __ldg(reinterpret_cast<const double2 *>(src + off + 16 * k * G));
-        dst[pass * CPP * GRB_SLOT_STRIDE + k * G] = p.x + p.y * t;
+        dst[pass * CPP * STRIDE + k * G] = p.x + p.y * t;
       }
     }
+  }
+}
+
+// cool_multi_time_g.F: one evaluation of the cooling rate, t_cool = max(p/(gamma-1), tiny)/edot.
+// Same structure as one subcycle of k_solve up to the cooling sums: per-cell temperature and
+// log-T bin, warp-cooperative coalesced fetch of the cooling-table row into shared-memory
+// slots (per-thread gathers kept the L1 at ~3/4 of its wavefront rate), log/exp table in
+// shared memory.  VAR: optional physics modules folded away at compile time, as for k_solve.
+#define GRB_CT_THREADS 128
+#define GRB_CT_STRIDE 25
+template <int PC, int VAR>
+__global__ void __launch_bounds__(GRB_CT_THREADS) k_cooling_time(const __grid_constant__ GrParams P0)
+{
+  __shared__ double ct_slots[GRB_CT_THREADS * GRB_CT_STRIDE];
+  __shared__ double ct_fm[GRB_FM_TABLE_DOUBLES];
+  for (int i = threadIdx.x; i < GRB_FM_TABLE_DOUBLES; i += GRB_CT_THREADS) ct_fm[i] = P0.fm_tab[i];
+  __syncthreads();
+  GrParams P = P0;
+  P.fm_tab = ct_fm;
+  variant_flags<VAR>(P);
+  const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
+  double *const my_slots = ct_slots + threadIdx.x * GRB_CT_STRIDE;
+  double *const warp_slots = ct_slots + (threadIdx.x & ~31u) * GRB_CT_STRIDE;
+
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = t < P.nactive;
+  Cell c;
+  Thermo th;
+  size_t x = 0;
+  double tgasold = 0.0, logtem = 0.0, tdef = 0.0;
+  int off = 0;
+  if (valid) {
+    int i, j, k;
+    x = cell_index(P, t, i, j, k);
+    load_cell<PC, true>(P, x, c, false);
+    logtem = thermo_head<PC>(P, c, true, tgasold, th, false);
+    if ((PC > 0) || (P.idustall > 0)) {           // cool1d_multi_g.F:349-357
+      const TIndex ti = t_index(P, logtem);
+      off = (ti.idx - 1) * (NCOOL * 16);
+      tdef = ti.tdef;
+    }
+  }
+  if (PC > 1 || anydust) coop_fetch<8, NCOOL, NCOOL * 16, GRB_CT_STRIDE>(P.cool, off, tdef, warp_slots);
+  else if (PC == 1) coop_fetch<4, L_BREM + 1, NCOOL * 16, GRB_CT_STRIDE>(P.cool, off, tdef, warp_slots);
+  __syncwarp();
+  if (valid) {
+    cool_sums<PC>(P, c, logtem, CoolSlots{my_slots}, tgasold, th);
+    const double energy = dmax(th.p2d * P.inv_gm1, GRB_TINY);
+    P.out[x] = ddiv_s(energy, th.edot);
   }
 }
 
