@@ -109,21 +109,21 @@ __global__ void __launch_bounds__(256) k_thermo(const __grid_constant__ GrParams
   if (PC > 1) { HM = P.f[F_HM][x]; H2I = P.f[F_H2I][x]; H2II = P.f[F_H2II][x]; }
 
   if (PC > 1) {   // H2 vibrational correction of the pressure
-    const double GammaInverse = 1.0 / (P.gamma - 1.0);
+    const double GammaInverse = P.inv_gm1;
     double number_density = 0.25 * (HeI + HeII + HeIII) + HI + HII + HM + de;
     const double nH2 = 0.5 * (H2I + H2II);
     if (number_density == 0) number_density = tiny_number;
-    const double temp = dmax(P.utem * p / (number_density + nH2), 1);
+    const double temp = dmax(ddiv_s(P.utem * p, number_density + nH2), 1);
     double GammaH2Inverse = 0.5 * 5.0;
-    if (nH2 / number_density > 1e-3) {
-      const double xx = 6100.0 / temp;
+    if (ddiv_s(nH2, number_density) > 1e-3) {
+      const double xx = ddiv_s(6100.0, temp);
       if (xx < 10.0) {
         const double ex = exp(xx);
         GammaH2Inverse = 0.5 * (5 + 2.0 * xx * xx * ex / ((ex - 1.0) * (ex - 1.0)));
       }
     }
-    const double Gamma1 = 1.0 + (nH2 + number_density) / (nH2 * GammaH2Inverse + number_density * GammaInverse);
-    p *= (Gamma1 - 1.0) / (P.gamma - 1.0);
+    const double Gamma1 = 1.0 + ddiv_s(nH2 + number_density, nH2 * GammaH2Inverse + number_density * GammaInverse);
+    p *= (Gamma1 - 1.0) * P.inv_gm1;
   }
   if (MODE == 0) { P.out[x] = p; return; }
 
@@ -131,23 +131,23 @@ __global__ void __launch_bounds__(256) k_thermo(const __grid_constant__ GrParams
   double number_density = 0.25 * (HeI + HeII + HeIII) + HI + HII + de;
   if (PC > 1) number_density += HM + 0.5 * (H2I + H2II);
   if (P.imetal == 1) number_density += P.f[F_METAL][x] * (1.0 / GRB_MU_METAL);
-  double T = p * (P.utem / dmax(number_density, 1. - 20));
+  double T = p * ddiv_s(P.utem, dmax(number_density, 1. - 20));
   T = dmax(T, 1.0);
   if (MODE == 1) { P.out[x] = T; return; }
 
   // gamma (only reached for PC > 1; PC <= 1 is a host-side fill)
-  const double GammaInverse = 1 / (P.gamma - 1.0);
+  const double GammaInverse = P.inv_gm1;
   number_density = 0.25 * (HeI + HeII + HeIII) + HI + HII + HM + de;
   const double nH2 = 0.5 * (H2I + H2II);
   double GammaH2Inverse = 0.5 * 5.0;
-  if (nH2 / number_density > 1e-3) {
-    const double xx = 6100.0 / T;
+  if (ddiv_s(nH2, number_density) > 1e-3) {
+    const double xx = ddiv_s(6100.0, T);
     if (xx < 10.0) {
       const double ex = exp(xx);
       GammaH2Inverse = 0.5 * (5 + 2.0 * xx * xx * ex / ((ex - 1.0) * (ex - 1.0)));
     }
   }
-  P.out[x] = 1.0 + (nH2 + number_density) / (nH2 * GammaH2Inverse + number_density * GammaInverse);
+  P.out[x] = 1.0 + ddiv_s(nH2 + number_density, nH2 * GammaH2Inverse + number_density * GammaInverse);
 }
 
 // constant fill of the active region (calculate_gamma for pc <= 1)
