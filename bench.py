@@ -34,7 +34,7 @@ SLAB = (1024, 1024, 128)            # (ni, nj, nk) per GPU
 BYTES_PER_CELL = 224                # 15 fields read + 13 written, FP64
 FLOP_PER_SUBCYCLE = 1050.0          # SURVEY 8d hand count for C4 (a5 360 + a7 170 + a8 185 + a9 340)
 FLOP_PER_CELL_FIXED = 60.0          # scale + ceiling + make_consistent
-TRAFFIC_PER_CELL_NCU = 219.3        # (dram__bytes_read + dram__bytes_write) / cells, profiles/r1_solve_v7_summary.txt
+TRAFFIC_PER_CELL_NCU = 213.5        # (dram__bytes_read + dram__bytes_write) / cells, profiles/r1_solve_final_summary.txt
 
 
 def load_peaks():
