@@ -250,6 +250,27 @@ def run_ours(args):
     elapsed = float(elapsed.item())
     value = world * ncell * args.steps / elapsed
 
+    # ---- size-independent properties of the full-size result (the last step's output) ----
+    # make_consistent_g: H, He and D nuclei and the electron density are exactly re-normalised
+    fh = float(ch.chem.HydrogenFractionByMass)
+    dtoh = float(ch.chem.DeuteriumToHydrogenRatio)
+    w = work
+    free = w["density"] - w["metal_density"]
+    Htot = w["HI_density"] + w["HII_density"] + w["HM_density"] + w["H2I_density"] + w["H2II_density"]
+    Hetot = w["HeI_density"] + w["HeII_density"] + w["HeIII_density"]
+    Dtot = w["DI_density"] + w["DII_density"] + (2.0 / 3.0) * w["HDI_density"]
+    de = (w["HII_density"] + w["HeII_density"] / 4 + w["HeIII_density"] / 2 - w["HM_density"]
+          + w["H2II_density"] / 2)
+    checks = {
+        "H_nuclei_max_rel": float(((Htot - fh * free).abs() / (fh * free)).max().item()),
+        "He_nuclei_max_rel": float(((Hetot - (1 - fh) * free).abs() / ((1 - fh) * free)).max().item()),
+        "D_nuclei_max_rel": float(((Dtot - fh * dtoh * free).abs() / (fh * dtoh * free)).max().item()),
+        "charge_max_rel": float(((w["e_density"] - de).abs() / de.abs()).max().item()),
+        "all_finite_positive": bool(all(bool(torch.isfinite(v).all().item()) and bool((v > 0).all().item())
+                                        for v in w.values())),
+    }
+    del free, Htot, Hetot, Dtot, de
+
     # ---- roofline of the dominant kernel (k_solve), from its own CUDA-event times ----
     # The solve is bound by the FP64 pipe, not by HBM or tensor cores (there is no dense
     # contraction on this path): `roofline` is therefore quoted against the measured non-tensor
@@ -352,7 +373,7 @@ def run_ours(args):
                        "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2" % (ncell * 120 / 1e9),
                        "mean_subcycles_per_cell": subs / ncell},
             "roofline": roofline, "roofline_hbm": roofline_hbm, "calculate_sweep": sweep, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": int(launches), "clocks": sampler.summary(),
+            "gpu_launches": int(launches), "clocks": sampler.summary(), "full_size_checks": checks,
             "diagnostics": {"subcycles_sum_all_ranks": int(diag[0].item()) if dist is not None else int(stats.subcycles_sum),
                             "cells_hit_itmax": int(diag[1].item()) if dist is not None else int(stats.cells_hit_itmax),
                             "cells_nan": int(diag[2].item()) if dist is not None else int(stats.cells_nan)},
