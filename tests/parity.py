@@ -19,8 +19,8 @@ def make_pair(product_lib, oracle_lib, params):
     return cp, co
 
 
-def make_grid(fields, dims, start=None, end=None, extra=None):
-    g = capi.Grid(dims, start=start, end=end)
+def make_grid(fields, dims, start=None, end=None, extra=None, dx=0.0):
+    g = capi.Grid(dims, start=start, end=end, dx=dx)
     keep = {}
     for k, v in fields.items():
         keep[k] = np.ascontiguousarray(v, dtype=np.float64).copy()
