@@ -4,9 +4,9 @@
 //
 //   k_pressure / k_temperature / k_gamma   calculate_{pressure,temperature,gamma}.c   HBM-bound
 //   k_temperature_table                    calc_temp_cloudy_g.F (pc = 0)              HBM + L2 gathers
-//   k_cooling_time                         cool_multi_time_g.F                        HBM + FP64
+//   k_cooling_time                         cool_multi_time_g.F                        FP64 + HBM
 //   k_dust_temperature                     calc_tdust_3d_g.F                          FP64 (Newton)
-//   k_solve                                solve_rate_cool_g.F (whole file)           FP64 pipe
+//   k_solve                                solve_rate_cool_g.F (whole file)           FP64 pipe / instruction issue
 //
 // No tensor cores: there is no dense contraction anywhere on this path (north_star).
 #include <cuda_runtime.h>
@@ -341,14 +341,15 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
   if (PC > 2) { P.f[F_DI][x] = c.DI; P.f[F_DII][x] = c.DII; P.f[F_HDI][x] = c.HDI; }
 }
 
-// CTA-wide re-alignment points.  The executed path of one subcycle is ~100 KB of SASS,
-// three times the SM's 32 KB instruction cache; warps that drift apart each stream it from
-// L2 on their own (ncu round 1: 55 % of all stall cycles were stall_no_inst).  A barrier per
-// subcycle keeps the warps of a group inside the same few KB of code, so one warp's fetch
-// serves all of them.
+// CTA-wide re-alignment points.  The executed path of one subcycle (31 KB of SASS in the
+// compact instantiation, 66 KB before round 1's code-size work) competes with a 32 KB
+// instruction cache; warps that drift apart each stream it from L2 on their own (first
+// version: 55 % of all stall cycles were stall_no_inst).  A barrier per subcycle keeps the
+// warps of a group inside the same few KB of code, so one warp's fetch serves all of them.
 // The CTA is split into lockstep groups of GRB_GROUP_WARPS warps, each on its own named
-// barrier: inside a group one warp's instruction fetch serves all, while the groups run out
-// of phase with each other so one group's barrier tail is covered by the others' work.
+// barrier.  With groups of 4 every SM sub-partition holds one warp of each group: the four
+// warps a scheduler sees are in different phases and cover each other's latencies.
+// Measured (Mcell/s, C4 sample): 1 warp 31.2, 2: 32.3, 4: 31.9, 8: 29.0, 16: 21.8.
 #ifndef GRB_GROUP_WARPS
 #define GRB_GROUP_WARPS 4
 #endif
