@@ -388,8 +388,9 @@ __device__ __forceinline__ bool group_any(int bar_id, bool pred)
 // pairs of columns g, g+G, g+2G, ... - each load instruction of the group covers G
 // consecutive 16-byte words - forms a + d * t and stores column c to slot c of that cell's row.
 // All loads of a pass are independent of each other.
-// (explicit load batches over passes and a group barrier only every 2nd/4th subcycle were
-// measured slower than letting the compiler schedule this loop.)
+// (explicit load batches over passes, a group barrier only every 2nd/4th subcycle, and passing
+// (weight, offset) through a shared-memory mailbox instead of the three shuffles were all
+// measured slower than this loop as the compiler schedules it.)
 template <int G, int NCOLS, int ROWB, int STRIDE = GRB_SLOT_STRIDE>
 __device__ __forceinline__ void coop_fetch(const double *table, int my_off, double my_t, double *dst0)
 {
