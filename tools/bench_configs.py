@@ -13,7 +13,10 @@ sys.path.insert(0, ROOT)
 from grackle_b200 import capi, synth_fields as sf, synth_tables  # noqa: E402
 
 n = 1 << (int(sys.argv[1]) if len(sys.argv) > 1 else 22)
+set_name = sys.argv[2] if len(sys.argv) > 2 else "B"
 lib = capi.load_product()
+if len(sys.argv) > 3 and sys.argv[3] == "general":
+    lib.grb200_set_solve_variant(1)      # force the general instantiation
 table = synth_tables.ensure()
 dev = torch.device("cuda", 0)
 for name in ("C1", "C2", "C3", "C4"):
@@ -21,7 +24,7 @@ for name in ("C1", "C2", "C3", "C4"):
     pc = params["primordial_chemistry"]
     ch = capi.Chemistry(lib, **params).initialize()
     idx = torch.arange(n, dtype=torch.int64, device=dev)
-    pristine = sf.make_fields(idx, pc, params, ch.temperature_units, "B")
+    pristine = sf.make_fields(idx, pc, params, ch.temperature_units, set_name)
     pristine = {k: v.contiguous() for k, v in pristine.items()}
     work = {k: torch.empty_like(v) for k, v in pristine.items()}
     g = capi.Grid([n])
@@ -37,6 +40,6 @@ for name in ("C1", "C2", "C3", "C4"):
         lib.grb200_last_solve_stats(C.byref(ch.rates), C.byref(st))
         ms.append(st.kernel_ms)
     t = min(ms[1:]) * 1e-3
-    print("%s pc=%d  %.2f Mcell/s  %.1f subcycles/cell  %.2f Gsubcycle/s  kernel %.1f ms"
-          % (name, pc, n / t / 1e6, st.subcycles_sum / n, st.subcycles_sum / t / 1e9, t * 1e3))
+    print("%s set %s pc=%d  %.2f Mcell/s  %.1f subcycles/cell  %.2f Gsubcycle/s  kernel %.1f ms"
+          % (name, set_name, pc, n / t / 1e6, st.subcycles_sum / n, st.subcycles_sum / t / 1e9, t * 1e3))
     ch.free()
