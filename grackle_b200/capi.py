@@ -177,6 +177,8 @@ def load_product():
     lib.grb200_measure_fp64_tflops.restype = C.c_double
     lib.grb200_set_solve_variant.argtypes = [C.c_int]
     lib.grb200_set_solve_variant.restype = None
+    lib.grb200_set_host_pipeline.argtypes = [C.c_int, C.c_longlong]
+    lib.grb200_set_host_pipeline.restype = None
     return lib
 
 

@@ -466,7 +466,51 @@ __global__ void __launch_bounds__(GRB_CT_THREADS) k_cooling_time(const __grid_co
   }
 }
 
-template <int PC>
+// ---- host-buffer pipeline hooks (GrParams::chunk_*; api.cu solve_pipelined) -----------
+// They are a template switch of the kernel, not a run-time one: merely present in the
+// subcycle loop they cost the device-resident path 2 % (measured), so that path runs
+// instantiations without them.
+// Per-lane state (the chunk of the cell in hand, the number
+// of chunks last seen ready) lives in the spare 41st slot of the lane's shared-memory row,
+// not in registers: the subcycle loop has none to give.
+// Wait until `chunk` has arrived: *count is the number of chunks whose copies are complete,
+// written by the copy stream behind each chunk's field copies.  Returns the count seen, or 0
+// after 20 s without progress so that a host-side failure cannot wedge the GPU.
+__device__ __forceinline__ unsigned chunk_wait(const unsigned *count, unsigned chunk)
+{
+  unsigned v;
+  unsigned long long t0 = 0;
+  for (;;) {
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(count) : "memory");
+    if (v > chunk) return v;
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > 20000000000ull) return 0u;
+    __nanosleep(500);
+  }
+}
+
+// Finished cells are counted per lane (lane_state[0] = chunk << 16 | finished cells of that
+// chunk not yet reported) and reported when the lane moves on to another chunk or leaves:
+// the report needs a fence behind the cell's stores, and a fence per finished cell sat on the
+// lockstep group's critical path (+4 % kernel time, measured).  The lane that completes the
+// chunk's count tells the host.
+__device__ __forceinline__ void chunk_report(const GrParams &P, unsigned state)
+{
+  const unsigned chunk = state >> 16, n = state & 0xffffu;
+  if (n == 0u) return;
+  const long long left = P.nactive - ((long long)chunk << P.chunk_shift);
+  const long long size = 1ll << P.chunk_shift;
+  const unsigned total = (unsigned)(left < size ? left : size);
+  __threadfence();                       // the cells' stores before the count
+  if (atomicAdd(P.chunk_done + chunk, n) + n == total) {
+    __threadfence_system();
+    *reinterpret_cast<volatile unsigned *>(P.chunk_done_host + chunk) = 1u;
+  }
+}
+
+template <int PC, bool PIPE>
 __device__ __forceinline__ void solve_cells(const GrParams &P)
 {
   extern __shared__ double slot_rows[];     // [GRB_SOLVE_THREADS][GRB_SLOT_STRIDE]
@@ -481,6 +525,8 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
   SubState s;
   size_t x = 0;
   bool active = false, exhausted = false;
+  unsigned *const lane_state = reinterpret_cast<unsigned *>(my_slots + NSLOT);   // [0] chunk | unreported, [1] chunks seen ready
+  if (PIPE) { lane_state[0] = 0u; lane_state[1] = 0u; }
   unsigned long long my_sub = 0, my_max = 0, my_itmax = 0, my_nan = 0;
 
   for (;;) {
@@ -496,17 +542,38 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
         if (t < P.nactive) {
           int ci, cj, ck;
           x = cell_index(P, t, ci, cj, ck);
-          bool run = true;
-          if (P.iradtrans == 1 && P.iradcoupled == 1) {   // coupled-RT masks (:418-439)
-            const bool lit = P.f[F_KPHHI][x] > 0;
-            run = (P.iradstep == 1) ? lit : !lit;
+          bool ready = true;
+          if (PIPE) {
+            const unsigned chunk = (unsigned)(t >> P.chunk_shift), state = lane_state[0];
+            if ((state >> 16) != chunk || (state & 0xffffu) == 0xffffu) {
+              chunk_report(P, state);
+              lane_state[0] = chunk << 16;
+            }
+            if (chunk >= lane_state[1]) ready = (lane_state[1] = chunk_wait(P.chunk_ready, chunk)) != 0u;
           }
-          load_cell<PC, false>(P, x, c, true);
-          s.ttot = 0.0; s.tgasold = 0.0; s.dedot_prev = 0.0; s.HIdot_prev = 0.0; s.iter = 1;
-          if (run) active = true;
-          else store_cell<PC>(P, x, c);     // masked cell: floors + consistency only
+          if (ready) {
+            bool run = true;
+            if (P.iradtrans == 1 && P.iradcoupled == 1) {   // coupled-RT masks (:418-439)
+              const bool lit = P.f[F_KPHHI][x] > 0;
+              run = (P.iradstep == 1) ? lit : !lit;
+            }
+            load_cell<PC, false>(P, x, c, true);
+            s.ttot = 0.0; s.tgasold = 0.0; s.dedot_prev = 0.0; s.HIdot_prev = 0.0; s.iter = 1;
+            if (run) active = true;
+            else {                            // masked cell: floors + consistency only
+              store_cell<PC>(P, x, c);
+              if (PIPE) lane_state[0] += 1u;
+            }
+          } else {                            // the host never delivered this chunk
+            atomicMax(P.diag + 5, 1ull);
+            exhausted = true;
+          }
         } else {
           exhausted = true;
+          if (PIPE) {                         // nothing more to come: report now, not at group exit
+            chunk_report(P, lane_state[0]);
+            lane_state[0] &= 0xffff0000u;
+          }
         }
       }
     }
@@ -564,6 +631,7 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
         if (s.iter > (int)my_max) my_max = s.iter;
         if (!(c.e == c.e) || !(c.HI == c.HI)) my_nan++;
         store_cell<PC>(P, x, c);
+        if (PIPE) lane_state[0] += 1u;
         active = false;
       } else {
         s.iter++;
@@ -571,6 +639,8 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
     }
     __syncwarp();
   }
+
+  if (PIPE) chunk_report(P, lane_state[0]);
 
   // ---- diagnostics: warp reduce, one atomic per warp ----
 #pragma unroll
@@ -614,7 +684,7 @@ __host__ __device__ inline void variant_flags(GrParams &P)
   if (VAR == VAR_LEAN) { P.idust = 0; P.iradshield = 0; }
 }
 
-template <int PC, int VAR>
+template <int PC, int VAR, bool PIPE>
 __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solve(const __grid_constant__ GrParams P0)
 {
   // the 2.5 KB log/exp table goes to shared memory behind the slot rows; the by-value copy of
@@ -626,7 +696,7 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
   GrParams P = P0;
   P.fm_tab = fm;
   variant_flags<VAR>(P);
-  solve_cells<PC>(P);
+  solve_cells<PC, PIPE>(P);
 }
 
 // ------------------------------------------------------------------------------
@@ -729,10 +799,15 @@ int grb_solve_variant_for(const GrParams &P)
 void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
 {
   const int var = grb_solve_variant_for(P);
-#define LAUNCH(PCV, V)                                                                                   \
-  {                                                                                                      \
-    cudaFuncSetAttribute(k_solve<PCV, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);  \
-    k_solve<PCV, V><<<blocks, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM, st>>>(P);                               \
+#define LAUNCH1(PCV, V, PIPE)                                                                                  \
+  {                                                                                                              \
+    cudaFuncSetAttribute(k_solve<PCV, V, PIPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);    \
+    k_solve<PCV, V, PIPE><<<blocks, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM, st>>>(P);                                 \
+  }
+#define LAUNCH(PCV, V)                                             \
+  {                                                                \
+    if (P.chunk_shift > 0) LAUNCH1(PCV, V, true)                   \
+    else LAUNCH1(PCV, V, false)                                    \
   }
 #define CALL(PCV)                                                   \
   if (var == VAR_LEAN) LAUNCH(PCV, VAR_LEAN)                        \
@@ -741,14 +816,15 @@ void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
 #undef LAUNCH
+#undef LAUNCH1
 }
 
 int grb_solve_max_blocks_per_sm(int pc)
 {
   int n = 0;
 #define CALL(PCV)                                                                                           \
-  cudaFuncSetAttribute(k_solve<PCV, VAR_GENERAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);   \
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV, VAR_GENERAL>, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM);
+  cudaFuncSetAttribute(k_solve<PCV, VAR_GENERAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRB_SOLVE_SMEM);   \
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_solve<PCV, VAR_GENERAL, true>, GRB_SOLVE_THREADS, GRB_SOLVE_SMEM);
   DISPATCH_PC(pc, CALL)
 #undef CALL
   return n;
