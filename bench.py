@@ -171,6 +171,8 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
+        # stdout carries the one JSON line only: NCCL's version banner goes to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
