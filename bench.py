@@ -25,6 +25,8 @@ import time
 
 import numpy as np
 
+_json_out = sys.stdout
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -156,7 +158,7 @@ def run_reference(args):
                                    "(no Fortran compiler on this image), OpenMP guided,1" % dims},
         "e2e": {"value": rate, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    print(json.dumps(line), file=_json_out)
 
 
 # ---------------------------------------------------------------------------------
@@ -171,8 +173,6 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        # stdout carries the one JSON line only: NCCL's version banner goes to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
@@ -382,7 +382,7 @@ def run_ours(args):
                             "cells_hit_itmax": int(diag[1].item()) if dist is not None else int(stats.cells_hit_itmax),
                             "cells_nan": int(diag[2].item()) if dist is not None else int(stats.cells_nan)},
         }
-        print(json.dumps(line))
+        print(json.dumps(line), file=_json_out)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -399,10 +399,18 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="skip the calculate_* (C5) timings")
     args = ap.parse_args()
+    # stdout carries the ONE JSON line and nothing else: native libraries (NCCL's version
+    # banner, the reference's own diagnostics) write to file descriptor 1 directly, so fd 1 is
+    # pointed at stderr for the whole run and the line goes to a duplicate of the real stdout.
+    global _json_out
+    sys.stdout.flush()
+    _json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
+    _json_out.flush()
 
 
 if __name__ == "__main__":
