@@ -265,7 +265,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
 
   if (P.imcool == 1) {   // Cloudy metal cooling (:1069-1097)
     if (P.clnew == 1) edot = edot + cloudy_edot(P, P.met, th.rhoH, th.metallicity, logtem, P.icmbTfloor, 1);
-    else edot = edot + cloudy_old_edot(P, P.met, c.d, th.rhoH, th.metallicity, logtem);
+    else edot = edot + cloudy_old_edot(P, P.met, c.d, c.de, th.rhoH, th.metallicity, logtem);
   }
 
   if (P.iVheat == 1) edot = edot + c.vheat / P.coolunit / (dom * dom);

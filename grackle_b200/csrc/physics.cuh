@@ -177,25 +177,71 @@ __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, do
   return edot_met * rhoH * rhoH;
 }
 
-// ---- old-style tables, rank <= 3 (cool1d_cloudy_old_tables_g.F; rank 4/5 need the
-// electron-fraction axis and are rejected on the host) ----------------------------
-__device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c, double d,
+// ---- interpolate_4D_g / interpolate_5D_g (interpolators_g.F:343-566) ----------------
+// One routine for any rank R: axis q is interpolated from the two results of axis q+1, the
+// last (fastest) axis from two neighbouring data values - the nesting, index clamping
+// (uniform-axis index clamped, weight not) and operation order of the reference's unrolled
+// rank-4 and rank-5 routines.  `flat` is the 0-based flat index of the corner chosen so far.
+template <int R, int Q>
+__device__ inline double interp_axis(const GrCloudyDev &c, const double *data, const double (&in)[R],
+                                     const long long (&ix)[R], long long flat)
+{
+  const double x0 = ld(c.par[Q] + ix[Q] - 1), x1 = ld(c.par[Q] + ix[Q]);
+  double v0, v1;
+  if constexpr (Q == R - 1) {
+    const long long at = flat * c.dim[Q] + ix[Q];     // 1-based position on the last axis
+    v0 = ld(data + at - 1);
+    v1 = ld(data + at);
+  } else {
+    v0 = interp_axis<R, Q + 1>(c, data, in, ix, flat * c.dim[Q] + ix[Q] - 1);
+    v1 = interp_axis<R, Q + 1>(c, data, in, ix, flat * c.dim[Q] + ix[Q]);
+  }
+  const double slope = (v1 - v0) / (x1 - x0);
+  return (in[Q] - x0) * slope + v0;
+}
+
+template <int R>
+__device__ __noinline__ double interp_rank(const GrCloudyDev &c, const double *data, const double (&in)[R])
+{
+  long long ix[R];
+#pragma unroll
+  for (int q = 0; q < R; q++) ix[q] = axis_index(in[q], c.par[q], c.dpar[q], c.dim[q]);
+  return interp_axis<R, 0>(c, data, in, ix, 0);
+}
+
+// ---- old-style tables, any rank 1..5 (cool1d_cloudy_old_tables_g.F:4-335).  Rank 4 adds the
+// electron-fraction axis, rank 5 the redshift axis in front of the temperature
+// (:138-146, :246-318); `de` is only read for those ranks. ---------------------------
+__device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c, double d, double de,
                                          double rhoH, double metallicity, double logtem)
 {
   const double log10_tCMB = P.log10_tcmb;        // see oracle note on the unassigned upstream local
   const double log10tem = logtem * GRB_INV_LN10;
-  double log_n_h = 0.0, log_Z = 0.0;
+  double log_n_h = 0.0, log_Z = 0.0, log_e_frac = 0.0, cl_e_frac = 1.0;
   if (c.rank > 1) log_n_h = DLOG10(rhoH * P.dom);
   if (c.rank > 2) log_Z = DLOG10(metallicity);
+  if (c.rank > 3) {                              // :138-146
+    const double fh = rhoH / d;
+    const double e_frac = 2.0 * de / (d * (1.0 + fh));
+    log_e_frac = dmin(log10(e_frac), 0.0);       // e_frac = 0 must give -Inf: library log10
+    cl_e_frac = e_frac * (1.0 + (2.0 * P.clEleFra * metallicity * fh) / (1.0 + fh));
+  }
   auto look = [&](const double *data, double lt) {
     if (c.rank == 1) return interp1(c, data, lt);
     if (c.rank == 2) return interp2(c, data, log_n_h, lt);
-    return interp3(c, data, log_n_h, log_Z, lt);
+    if (c.rank == 3) return interp3(c, data, log_n_h, log_Z, lt);
+    if (c.rank == 4) {
+      const double in[4] = {log_n_h, log_Z, log_e_frac, lt};
+      return interp_rank<4>(c, data, in);
+    }
+    const double in[5] = {log_n_h, log_Z, log_e_frac, P.zr, lt};
+    return interp_rank<5>(c, data, in);
   };
   double edot_met = -DEXP10(look(c.cooling, log10tem));
   if (P.icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
     edot_met = edot_met + DEXP10(look(c.cooling, log10_tCMB));
   if (P.iClHeat == 1) edot_met = edot_met + DEXP10(look(c.heating, log10tem));
+  if (c.rank > 3) edot_met = edot_met * cl_e_frac;
   return edot_met * rhoH * d;
 }
 

@@ -130,3 +130,83 @@ def ensure(path=None):
     if not os.path.exists(path):
         write(path)
     return path
+
+
+# ---------------------------------------------------------------------------------------
+# Old-style metal tables of rank 4 and 5 (cool1d_cloudy_old_tables_g.F; the reference's
+# `cloudy_metals_2008_{4,5}D.h5` family is not in the snapshot, only the rank-3 file is).
+# Same on-disk schema as cloudy_metals_2008_3D.h5: root attribute `old_style`,
+# /CoolingRates/Metals/{Cooling,Heating} with Rank / Dimension / Parameter1..Parameter(R-1) /
+# Temperature attributes.  Axes: log10 n_H, log10 Z/Zsun, log10 electron fraction,
+# [redshift], T.  /UVBRates is carried along so that UVbackground = 1 (which is what makes
+# the loader read Heating) can be used with these files.
+# ---------------------------------------------------------------------------------------
+OLD_DIMS = {4: (8, 5, 6, 33), 5: (8, 5, 6, 7, 33)}
+
+
+def build_old_style(rank):
+    assert rank in (4, 5)
+    dims = OLD_DIMS[rank]
+    log_nh = np.linspace(-6.0, 4.0, dims[0])
+    log_z = np.linspace(-4.0, 1.0, dims[1])
+    log_ef = np.linspace(-5.0, 0.0, dims[2])
+    T = 10.0 ** np.linspace(1.0, 8.0, dims[-1])
+    axes = [log_nh, log_z, log_ef]
+    if rank == 5:
+        axes.append(np.linspace(0.0, 9.0, dims[3]))
+    axes.append(T)
+    shape = [1] * rank
+    g = []
+    for q, ax in enumerate(axes):
+        sh = list(shape)
+        sh[q] = len(ax)
+        g.append((np.log10(ax) if q == rank - 1 else ax).reshape(sh))
+    nh, lz, ef, lt = g[0], g[1], g[2], g[-1]
+    zz = g[3] if rank == 5 else 0.0 * nh
+    uv = _uvb_shape(zz)
+    peak = -21.9 - 0.5 * ((lt - 5.2) / 0.9) ** 2 / (1.0 + 0.25 * np.abs(lt - 5.2))
+    fine = -26.1 + 0.8 * np.tanh((lt - 2.0) / 0.8) - 0.04 * (nh + 2.0)
+    cool = np.log10(10.0 ** peak + 10.0 ** fine) + 1.0 * lz - 0.35 * ef * (1.0 + 0.05 * lt)
+    cool = cool + 0.03 * np.sin(1.3 * lt + 0.4 * nh + 0.7 * lz) * np.cos(0.5 * ef + 0.6 * zz)
+    cool = cool - 0.1 * uv / (1.0 + 10.0 ** (nh + 2.0))
+    heat = -25.0 + np.log10(uv) + 1.0 * lz - 0.5 * np.log10(1.0 + 10.0 ** (nh + 3.0)) \
+        - 0.06 * (lt - 4.0) ** 2 + 0.2 * ef
+    cool = np.broadcast_to(cool, dims)
+    heat = np.broadcast_to(heat, dims)
+    return axes, 10.0 ** cool, 10.0 ** heat
+
+
+def write_old_style(path, rank):
+    axes, cool, heat = build_old_style(rank)
+    _, _, uvb = build_tables()
+    dims = np.array(cool.shape, dtype=np.int64)
+    attrs = {"Rank": np.int64(rank), "Dimension": dims}
+    for q, ax in enumerate(axes):
+        attrs["Temperature" if q == rank - 1 else "Parameter%d" % (q + 1)] = np.ascontiguousarray(ax)
+    g = h5lite.Group()
+    g["Cooling"] = h5lite.Dataset(np.ascontiguousarray(cool, dtype=np.float64), dict(attrs))
+    g["Heating"] = h5lite.Dataset(np.ascontiguousarray(heat, dtype=np.float64), dict(attrs))
+    cr = h5lite.Group()
+    cr["Metals"] = g
+    root = h5lite.Group(attrs={"old_style": np.int64(1)})
+    root["CoolingRates"] = cr
+    ub = h5lite.Group()
+    ub["Info"] = h5lite.Dataset("SYNTHETIC UV background (grackle-b200 synth_tables.py)")
+    ub["z"] = h5lite.Dataset(uvb["z"])
+    for sub in ("Chemistry", "Photoheating", "CrossSections"):
+        sg = h5lite.Group()
+        for k, v in uvb.items():
+            if k.startswith(sub + "/"):
+                sg[k.split("/")[1]] = h5lite.Dataset(np.ascontiguousarray(v, dtype=np.float64))
+        ub[sub] = sg
+    root["UVBRates"] = ub
+    h5lite.write_file(path, root)
+    return path
+
+
+def ensure_old_style(rank):
+    d = os.path.dirname(default_path())
+    path = os.path.join(d, "cloudy_metals_SYNTHETIC_%dD.h5" % rank)
+    if not os.path.exists(path):
+        write_old_style(path, rank)
+    return path

@@ -1,14 +1,14 @@
 """GPU parity over the parameter space around the BASELINE configurations (SURVEY 8f ranks
 1-3: dust physics, radiative-transfer fields, H2 / UVB self-shielding options, three-body
 rates, Case B, CIE, optical-depth fudge, Compton X-ray, Lyman-Werner background, extra
-heating fields).  Every variant runs the GENERAL instantiation of the solve kernel (or the
+heating fields, old-style rank-4/5 metal tables).  Every variant runs the GENERAL instantiation of the solve kernel (or the
 dust+shielding one) against the CPU oracle on identical inputs, plus calculate_cooling_time.
 """
 import numpy as np
 import pytest
 
 import parity
-from grackle_b200 import capi, synth_fields as sf
+from grackle_b200 import capi, synth_fields as sf, synth_tables
 
 pytestmark = pytest.mark.gpu
 
@@ -67,6 +67,13 @@ VARIANTS = [
                                    self_shielding_method=0), ("isrf",), True),
     ("pe_heating_1", "C2", dict(photoelectric_heating=1, photoelectric_heating_rate=8.5e-26), (), False),
     ("pe_heating_3", "C3", dict(dust_chemistry=1, photoelectric_heating=3, self_shielding_method=0), (), False),
+    # old-style metal tables with the electron-fraction axis (rank 4) and electron fraction +
+    # redshift (rank 5): interpolate_4D_g / interpolate_5D_g (synthetic files, same schema as
+    # cloudy_metals_2008_3D.h5); `_old_rank` is consumed by the test, not a Grackle parameter
+    ("old_tables_rank4", "C2", dict(_old_rank=4), (), False),
+    ("old_tables_rank4_pc3", "C4", dict(_old_rank=4, cmb_temperature_floor=0), (), False),
+    ("old_tables_rank5", "C4", dict(_old_rank=5), (), False),
+    ("old_tables_rank5_no_uvb", "C2", dict(_old_rank=5, UVbackground=0), (), False),
 ]
 
 
@@ -75,6 +82,9 @@ def test_variant_parity(product_lib, oracle_lib, synth_table, vid, base, over, e
     params, dt, _ = sf.config(base, synth_table)
     params = dict(params)
     params.update(over)
+    old_rank = params.pop("_old_rank", 0)
+    if old_rank:
+        params["grackle_data_file"] = synth_tables.ensure_old_style(old_rank)
     cp, co = parity.make_pair(product_lib, oracle_lib, params)
     try:
         idx = np.arange(N, dtype=np.int64)
