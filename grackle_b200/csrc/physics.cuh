@@ -183,7 +183,7 @@ __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, do
 // (uniform-axis index clamped, weight not) and operation order of the reference's unrolled
 // rank-4 and rank-5 routines.  `flat` is the 0-based flat index of the corner chosen so far.
 template <int R, int Q>
-__device__ inline double interp_axis(const GrCloudyDev &c, const double *data, const double (&in)[R],
+__device__ __forceinline__ double interp_axis(const GrCloudyDev &c, const double *data, const double (&in)[R],
                                      const long long (&ix)[R], long long flat)
 {
   const double x0 = ld(c.par[Q] + ix[Q] - 1), x1 = ld(c.par[Q] + ix[Q]);
@@ -200,8 +200,12 @@ __device__ inline double interp_axis(const GrCloudyDev &c, const double *data, c
   return (in[Q] - x0) * slope + v0;
 }
 
+// (force-inlined on purpose: a real call would take the address of a member of the kernel's
+// by-value parameter copy, which sends the whole copy - and with it every instantiation of
+// the solve kernel, including the ones where this code is dead - to local memory: the compact
+// solve kernel ran 2.15x slower with a 1952-byte stack frame)
 template <int R>
-__device__ __noinline__ double interp_rank(const GrCloudyDev &c, const double *data, const double (&in)[R])
+__device__ __forceinline__ double interp_rank(const GrCloudyDev &c, const double *data, const double (&in)[R])
 {
   long long ix[R];
 #pragma unroll

@@ -242,3 +242,26 @@ print("FAILS-LOUDLY-OK")
     assert r.returncode == 0, r.stderr[-2000:]
     assert "FAILS-LOUDLY-OK" in r.stdout
     assert "grackle-b200" in r.stderr          # the diagnostic names the library
+
+
+def test_compact_solve_kernels_keep_their_state_in_registers():
+    """Resource usage of the built sm_100a kernels (cuobjdump, no GPU needed).  The compact
+    (LEAN) solve kernels must not fall back to a local-memory copy of the kernel parameters:
+    a device function that takes the address of a member of the by-value GrParams copy and is
+    NOT inlined does exactly that, for every instantiation, and once cost the headline kernel
+    2.15x (1952-byte stack frame) without failing any parity test."""
+    import shutil
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not available")
+    so = os.path.join(ROOT, "grackle_b200", "lib", "libgrackle_b200.so")
+    out = subprocess.run(["cuobjdump", "-res-usage", so], capture_output=True, text=True).stdout
+    usage = {m[0]: (int(m[1]), int(m[2]))
+             for m in re.findall(r"Function (\S+):\s*\n\s*REG:(\d+) STACK:(\d+)", out)}
+    lean = {k: v for k, v in usage.items() if re.search(r"k_solveILi[0-3]ELi1ELb[01]E", k)}
+    assert len(lean) == 8, sorted(usage)
+    for name, (reg, stack) in lean.items():
+        assert reg <= 128, (name, reg)       # 512 threads per SM need <= 128 registers
+        assert stack <= 64, (name, stack)
+    for name, (reg, stack) in usage.items():
+        if "k_solve" in name:
+            assert reg <= 128 and stack <= 512, (name, reg, stack)
