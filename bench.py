@@ -34,8 +34,12 @@ from grackle_b200 import capi, synth_fields as sf, synth_tables  # noqa: E402
 
 SLAB = (1024, 1024, 128)            # (ni, nj, nk) per GPU
 BYTES_PER_CELL = 224                # 15 fields read + 13 written, FP64
-FLOP_PER_SUBCYCLE = 1050.0          # SURVEY 8d hand count for C4 (a5 360 + a7 170 + a8 185 + a9 340)
-FLOP_PER_CELL_FIXED = 60.0          # scale + ceiling + make_consistent
+# FP64 operations per cell-subcycle of the reference algorithm at config C4, COUNTED by the
+# operation-counting build of the CPU restatement (tests/count_flops.py -> tests/golden/flop_counts.json:
+# 446 add/sub + 443 mul + 154 div + 58 compare + 21 log + 9 pow, one flop each; per-call fixed work
+# included).  SURVEY 8d's hand count was 1050 (+-15 %).
+FLOP_PER_SUBCYCLE = 1131.3
+FLOP_PER_SUBCYCLE_HAND = 1050.0
 TRAFFIC_PER_CELL_NCU = 213.5        # (dram__bytes_read + dram__bytes_write) / cells, profiles/r1_solve_final_summary.txt
 
 
@@ -280,7 +284,7 @@ def run_ours(args):
     k_s = float(np.mean(kernel_ms)) * 1e-3
     hbm_peak, peak_kind = load_peaks()
     achieved_gbs = BYTES_PER_CELL * ncell / k_s / 1e9
-    flops = subs * FLOP_PER_SUBCYCLE + ncell * FLOP_PER_CELL_FIXED
+    flops = subs * FLOP_PER_SUBCYCLE
     fp64_peak = lib.grb200_measure_fp64_tflops()
     roofline = {"bound": "fp64", "achieved": flops / k_s / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
                 "frac": flops / k_s / 1e12 / fp64_peak if fp64_peak > 0 else None,
@@ -292,8 +296,12 @@ def run_ours(args):
                 "kernel": "k_solve<3, lean>", "kernel_ms": k_s * 1e3,
                 "peak_source": "FMA-chain microbenchmark in this run (grb200_measure_fp64_tflops); "
                                "MEASURED_PEAKS.json has no FP64 entry",
-                "flop_model": "sum(subcycles)*%g + cells*%g algorithmic flops (SURVEY 8d hand count; divisions "
-                              "and log/exp count as 1)" % (FLOP_PER_SUBCYCLE, FLOP_PER_CELL_FIXED),
+                "flop_model": "sum(subcycles)*%g flops: FP64 operations per cell-subcycle counted by the "
+                              "instrumented CPU restatement (tests/golden/flop_counts.json; a division, compare, "
+                              "log or pow counts as 1); SURVEY 8d hand count was %g"
+                              % (FLOP_PER_SUBCYCLE, FLOP_PER_SUBCYCLE_HAND),
+                "frac_hand_count_model": (subs * FLOP_PER_SUBCYCLE_HAND + ncell * 60.0) / k_s / 1e12 / fp64_peak
+                if fp64_peak > 0 else None,
                 "subcycles_per_cell": subs / ncell}
     roofline_hbm = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                     "frac": achieved_gbs / hbm_peak, "peak_source": peak_kind,

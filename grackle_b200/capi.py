@@ -182,11 +182,16 @@ def load_product():
     return lib
 
 
-def load_oracle():
-    """Load the CPU oracle (tests / smoke / bench CPU-baseline only)."""
-    if not os.path.exists(ORACLE_SO):
-        raise ExtensionMissing("oracle library %s is missing (make -C oracle)" % ORACLE_SO)
-    lib = _declare(C.CDLL(ORACLE_SO, mode=C.RTLD_LOCAL))
+def load_oracle(counting=False):
+    """Load the CPU oracle (tests / smoke / bench CPU-baseline only).  counting=True loads the
+    operation-counting build of the same code (oracle/flopcount.hpp)."""
+    so = ORACLE_SO.replace("libgrackle_oracle.so", "libgrackle_oracle_count.so") if counting else ORACLE_SO
+    if not os.path.exists(so):
+        raise ExtensionMissing("oracle library %s is missing (make -C oracle)" % so)
+    lib = _declare(C.CDLL(so, mode=C.RTLD_LOCAL))
+    if counting:
+        lib.oracle_flop_counts.argtypes = [C.POINTER(C.c_longlong), C.c_int]
+        lib.oracle_flop_counts.restype = None
     lib.oracle_inject_cloudy.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong),
                                          C.POINTER(c_dp), c_dp, c_dp, c_dp]
     lib.oracle_inject_cloudy.restype = None

@@ -38,6 +38,18 @@
 #include <vector>
 #include <algorithm>
 
+#ifdef ORACLE_COUNT_FLOPS
+// operation-counting build (oracle/flopcount.hpp, tools/count_flops.py): every `double` below
+// becomes a counting wrapper of identical layout; results are unchanged
+#include "flopcount.hpp"
+long long flopcount::n[flopcount::NKIND];
+extern "C" void oracle_flop_counts(long long *out, int reset)
+{
+  for (int i = 0; i < flopcount::NKIND; i++) { out[i] = flopcount::n[i]; if (reset) flopcount::n[i] = 0; }
+}
+#define double cd
+#endif
+
 namespace {
 
 typedef long long i8;
