@@ -38,3 +38,56 @@ def allreduce_diagnostics(stats, dist=None, device=None):
     s = [int(v) for v in sums.tolist()]
     return {"subcycles_sum": s[0], "cells_hit_itmax": s[1], "cells_nan": s[2], "cells": s[3],
             "subcycles_max": int(mx.item())}
+
+
+# ---------------------------------------------------------------------------------------
+# H2_self_shielding = 1 is the one option of the path with a neighbour stencil: the
+# Sobolev-like shielding length reads the DENSITY of the six neighbours
+# (solve_rate_cool_g.F:1418-1434).  A k-slab then carries one ghost plane beyond each
+# interior face, the active region is restricted with grid_start / grid_end (which the API
+# supports), and the density ghost planes are filled from the neighbouring ranks
+# before the solve.  Density is never written by the solve, so this is one exchange of two
+# planes per call and the only data-path communication of the whole path.
+# ---------------------------------------------------------------------------------------
+def halo_slab_layout(dims, world, rank, ghost_lo=0, ghost_hi=0):
+    """Layout of rank's slab of a (ni, nj, nk) grid whose ACTIVE planes are
+    ghost_lo <= k < nk - ghost_hi (the caller's own boundary layers count as ghost planes).
+    Returns dict: k0, k1 = planes held locally (owned planes plus one ghost plane per face),
+    dims = local grid dimensions, k_start, k_end = inclusive local active k range,
+    has_lo / has_hi = a neighbouring rank owns the plane below / above."""
+    ni, nj, nk = dims
+    a0, a1 = slab_bounds(nk - ghost_lo - ghost_hi, world, rank)
+    a0, a1 = a0 + ghost_lo, a1 + ghost_lo                 # owned (active) planes [a0, a1)
+    k0, k1 = max(a0 - 1, 0), min(a1 + 1, nk)
+    return {"k0": k0, "k1": k1, "dims": [ni, nj, k1 - k0], "k_start": a0 - k0, "k_end": a1 - 1 - k0,
+            "has_lo": rank > 0, "has_hi": rank < world - 1, "owned": (a0, a1)}
+
+
+def exchange_density_halo(density, layout, dist, rank):
+    """density: this rank's flat local array (torch tensor, ni*nj*(k1-k0)) whose ghost planes
+    facing other ranks are stale.  Sends the first / last OWNED plane to the lower / upper
+    neighbour and receives their planes into the ghost planes (point-to-point, NCCL over NVLink
+    on GPUs, gloo in the CPU test).  Even ranks send first, odd ranks receive first."""
+    ni, nj, _ = layout["dims"]
+    plane = ni * nj
+    ks, ke = layout["k_start"], layout["k_end"]
+
+    def own(k):
+        return density[k * plane:(k + 1) * plane]
+
+    # a chain of blocking sends cannot deadlock when neighbours alternate their order
+    if rank % 2 == 0:
+        if layout["has_hi"]:
+            dist.send(own(ke).contiguous(), rank + 1)
+            dist.recv(own(ke + 1), rank + 1)
+        if layout["has_lo"]:
+            dist.send(own(ks).contiguous(), rank - 1)
+            dist.recv(own(ks - 1), rank - 1)
+    else:
+        if layout["has_lo"]:
+            dist.recv(own(ks - 1), rank - 1)
+            dist.send(own(ks).contiguous(), rank - 1)
+        if layout["has_hi"]:
+            dist.recv(own(ke + 1), rank + 1)
+            dist.send(own(ke).contiguous(), rank + 1)
+    return density
