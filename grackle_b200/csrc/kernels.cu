@@ -350,8 +350,14 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 // barrier.  With groups of 4 every SM sub-partition holds one warp of each group: the four
 // warps a scheduler sees are in different phases and cover each other's latencies.
 // Measured (Mcell/s, C4 sample): 1 warp 31.2, 2: 32.3, 4: 31.9, 8: 29.0, 16: 21.8.
+// The best group size depends on how much code a subcycle streams: the compact instantiation
+// (5.6k instructions) is fastest with 2 warps per group (C1 +3 %, C2 +10 %, C4 +2 % over 4),
+// the larger dust + shielding and general ones with 4 (C3 -5 % with 2).
 #ifndef GRB_GROUP_WARPS
 #define GRB_GROUP_WARPS 4
+#endif
+#ifndef GRB_GROUP_WARPS_LEAN
+#define GRB_GROUP_WARPS_LEAN 2
 #endif
 // lanes per cell in the cooperative table fetches (fewer lanes = more loads per lane and pass)
 #ifndef GRB_G_MAIN
@@ -364,17 +370,20 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 #define GRB_G_DD 4
 #endif
 
-static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0, "CTA must be whole lockstep groups");
-static_assert(GRB_GROUP_WARPS == 1 || GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15, "named barriers 1..15");
+static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0 && GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS_LEAN) == 0,
+              "CTA must be whole lockstep groups");
+static_assert((GRB_GROUP_WARPS == 1 || GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15) &&
+              (GRB_GROUP_WARPS_LEAN == 1 || GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS_LEAN) <= 15), "named barriers 1..15");
 
 // barrier + OR-reduction of a predicate over the group
+template <int GW>
 __device__ __forceinline__ bool group_any(int bar_id, bool pred)
 {
   int out;
   asm volatile(
       "{\n\t.reg .pred p, q;\n\tsetp.ne.s32 q, %3, 0;\n\tbar.red.or.pred p, %1, %2, q;\n\tselp.s32 %0, 1, 0, p;\n\t}"
       : "=r"(out)
-      : "r"(bar_id), "r"(32 * GRB_GROUP_WARPS), "r"((int)pred)
+      : "r"(bar_id), "r"(32 * GW), "r"((int)pred)
       : "memory");
   return out != 0;
 }
@@ -388,7 +397,8 @@ __device__ __forceinline__ bool group_any(int bar_id, bool pred)
 // pairs of columns g, g+G, g+2G, ... - each load instruction of the group covers G
 // consecutive 16-byte words - forms a + d * t and stores column c to slot c of that cell's row.
 // All loads of a pass are independent of each other.
-// (explicit load batches over passes, a group barrier only every 2nd/4th subcycle, and passing
+// (explicit load batches over passes, a group barrier only every 2nd/4th subcycle, a
+// prefetch.global.L1 of the stage-4 chemistry row issued before stage 2 (-4 %), and passing
 // (weight, offset) through a shared-memory mailbox instead of the three shuffles were all
 // measured slower than this loop as the compiler schedules it.)
 template <int G, int NCOLS, int ROWB, int STRIDE = GRB_SLOT_STRIDE>
@@ -527,7 +537,7 @@ __device__ __forceinline__ void chunk_report(const GrParams &P, unsigned state)
   }
 }
 
-template <int PC, bool PIPE>
+template <int PC, bool PIPE, int GW>
 __device__ __forceinline__ void solve_cells(const GrParams &P)
 {
   extern __shared__ double slot_rows[];     // [GRB_SOLVE_THREADS][GRB_SLOT_STRIDE]
@@ -536,7 +546,7 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
   const Rates r{my_slots};
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const int bar_id = 1 + (int)(threadIdx.x >> 5) / GRB_GROUP_WARPS;
+  const int bar_id = 1 + (int)(threadIdx.x >> 5) / GW;
   const bool anydust = (P.idust > 0) || (P.idustall > 0) || (P.idustrec > 0);
   Cell c;
   SubState s;
@@ -595,7 +605,7 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
       }
     }
     // after the refill every lane either owns a cell or has seen the end of the queue
-    if (GRB_GROUP_WARPS == 1 ? !__any_sync(full, active) : !group_any(bar_id, active)) break;
+    if (GW == 1 ? !__any_sync(full, active) : !group_any<GW>(bar_id, active)) break;
 
     // ---- one subcycle on every busy lane ----
     // stage 1 (per cell): temperature and the two log-T bins.  Idle lanes point at bin 1.
@@ -713,7 +723,7 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
   GrParams P = P0;
   P.fm_tab = fm;
   variant_flags<VAR>(P);
-  solve_cells<PC, PIPE>(P);
+  solve_cells<PC, PIPE, (VAR == VAR_LEAN) ? GRB_GROUP_WARPS_LEAN : GRB_GROUP_WARPS>(P);
 }
 
 // ------------------------------------------------------------------------------
