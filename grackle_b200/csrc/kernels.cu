@@ -359,6 +359,11 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 #ifndef GRB_GROUP_WARPS_LEAN
 #define GRB_GROUP_WARPS_LEAN 2
 #endif
+// ... and the compact kernels of the two smallest networks (pc = 0, 1) with no grouping at all
+// (C1 +3 %, C2 +9 % over groups of 2; C4 -4 %)
+#ifndef GRB_GROUP_WARPS_LEAN_SMALL
+#define GRB_GROUP_WARPS_LEAN_SMALL 1
+#endif
 // lanes per cell in the cooperative table fetches (fewer lanes = more loads per lane and pass)
 #ifndef GRB_G_MAIN
 #define GRB_G_MAIN 8
@@ -723,7 +728,7 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
   GrParams P = P0;
   P.fm_tab = fm;
   variant_flags<VAR>(P);
-  solve_cells<PC, PIPE, (VAR == VAR_LEAN) ? GRB_GROUP_WARPS_LEAN : GRB_GROUP_WARPS>(P);
+  solve_cells<PC, PIPE, (VAR != VAR_LEAN) ? GRB_GROUP_WARPS : (PC <= 1) ? GRB_GROUP_WARPS_LEAN_SMALL : GRB_GROUP_WARPS_LEAN>(P);
 }
 
 // ------------------------------------------------------------------------------
