@@ -462,6 +462,7 @@ int fill_params(GrParams &P, DeviceCtx *ctx, const chemistry_data *chem,
   P.z_solar = chem->SolarMetalFractionByMass; P.fgr = chem->local_dust_to_gas_ratio;
   P.dtemstart = chem->DustTemperatureStart; P.dtemend = chem->DustTemperatureEnd;
   P.clEleFra = chem->cloudy_electron_fraction_factor;
+  P.iold45 = (chem->metal_cooling == 1 && rates->cloudy_data_new == 0 && rates->cloudy_metal.grid_rank > 3) ? 1 : 0;
   P.k24 = uvb.k24; P.k25 = uvb.k25; P.k26 = uvb.k26; P.k27 = uvb.k27; P.k28 = uvb.k28;
   P.k29 = uvb.k29; P.k30 = uvb.k30; P.k31 = uvb.k31;
   P.compa = rates->comp; P.gammaha = rates->gammah; P.isrf = chem->interstellar_radiation_field;

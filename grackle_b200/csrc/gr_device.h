@@ -86,6 +86,7 @@ struct GrParams {
   // flags
   int icool, ispecies, imetal, imcool, idust, idustall, idustfield, idustrec, igammah, iexpand;
   int ih2co, ipiht, ih2optical, iciecool, ithreebody, icmbTfloor, iClHeat, clnew;
+  int iold45;   // old-style metal table of rank 4 or 5 (electron-fraction / redshift axes): own instantiation
   int iH2shield, iradshield, iradtrans, iradcoupled, iradstep, irt_honly;
   int iVheat, iMheat, iisrffield, iH2shieldcustom, itmax, exititmax;
   int nratec, ndratec;

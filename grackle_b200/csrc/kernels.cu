@@ -703,11 +703,16 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
 //   VAR_DUST_SHIELD  VAR_LEAN + H2 formation on dust (h2_on_dust, no dust field) + UVB
 //                    self-shielding, any method (config C3)
 // grb_solve_variant_for() is the host-side choice; anything else runs VAR_GENERAL.
-enum { VAR_GENERAL = 0, VAR_LEAN = 1, VAR_DUST_SHIELD = 2 };
+enum { VAR_GENERAL = 0, VAR_LEAN = 1, VAR_DUST_SHIELD = 2, VAR_RANK45 = 3 };
 
 template <int VAR>
 __host__ __device__ inline void variant_flags(GrParams &P)
 {
+  // VAR_RANK45 = VAR_GENERAL + old-style metal tables of rank 4/5: their 16- and 32-corner
+  // interpolation (three lookups per subcycle) costs every general run up to 20 % through
+  // register pressure when it is merely compiled in, so it gets its own instantiation
+  if (VAR == VAR_RANK45) return;
+  P.iold45 = 0;
   if (VAR == VAR_GENERAL) return;
   P.idustall = 0; P.idustfield = 0; P.idustrec = 0; P.igammah = 0; P.ih2optical = 0;
   P.iciecool = 0; P.ithreebody = 0; P.iH2shield = 0; P.iradtrans = 0; P.iradcoupled = 0;
@@ -796,6 +801,7 @@ void grb_launch_cooling_time(const GrParams &P, cudaStream_t st)
 #define CALL(PCV)                                                                      \
   if (var == VAR_LEAN) k_cooling_time<PCV, VAR_LEAN><<<nb, 128, 0, st>>>(P);           \
   else if (var == VAR_DUST_SHIELD) k_cooling_time<PCV, VAR_DUST_SHIELD><<<nb, 128, 0, st>>>(P); \
+  else if (var == VAR_RANK45) k_cooling_time<PCV, VAR_RANK45><<<nb, 128, 0, st>>>(P);            \
   else k_cooling_time<PCV, VAR_GENERAL><<<nb, 128, 0, st>>>(P);
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
@@ -814,6 +820,7 @@ int grb_solve_variant = 0;
 // which instantiation serves this parameter set (VAR_* above)
 int grb_solve_variant_for(const GrParams &P)
 {
+  if (P.iold45 != 0) return VAR_RANK45;
   if (grb_solve_variant != 0) return VAR_GENERAL;
   // "off" is <= 0 for every switch (unset options stay at -1, e.g. dust_recombination_cooling)
   const bool off = P.idustall <= 0 && P.idustfield <= 0 && P.idustrec <= 0 && P.igammah <= 0 &&
@@ -844,6 +851,7 @@ void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st)
 #define CALL(PCV)                                                   \
   if (var == VAR_LEAN) LAUNCH(PCV, VAR_LEAN)                        \
   else if (var == VAR_DUST_SHIELD) LAUNCH(PCV, VAR_DUST_SHIELD)     \
+  else if (var == VAR_RANK45) LAUNCH(PCV, VAR_RANK45)               \
   else LAUNCH(PCV, VAR_GENERAL)
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL

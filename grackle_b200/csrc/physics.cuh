@@ -182,9 +182,23 @@ __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, do
 // last (fastest) axis from two neighbouring data values - the nesting, index clamping
 // (uniform-axis index clamped, weight not) and operation order of the reference's unrolled
 // rank-4 and rank-5 routines.  `flat` is the 0-based flat index of the corner chosen so far.
+// The axes travel BY VALUE in a small struct and the routine is a real (non-inlined) call:
+//  * a reference into the kernel's by-value parameter copy would take the address of that
+//    copy and send ALL of it - in every instantiation of the solve kernel, also where this
+//    code is dead - to local memory (measured: 1952-byte stack frame, compact kernel 2.15x
+//    slower);
+//  * inlined, the 31 nested interpolations of three lookups cost the general instantiation
+//    up to 19 % (C2) through code size and register pressure, for a table format almost no
+//    run uses.
+struct InterpAxes {
+  const double *par[5];
+  long long dim[5];
+  double dpar[5];
+};
+
 template <int R, int Q>
-__device__ __forceinline__ double interp_axis(const GrCloudyDev &c, const double *data, const double (&in)[R],
-                                     const long long (&ix)[R], long long flat)
+__device__ __forceinline__ double interp_axis(const InterpAxes &c, const double *data, const double (&in)[R],
+                                              const long long (&ix)[R], long long flat)
 {
   const double x0 = ld(c.par[Q] + ix[Q] - 1), x1 = ld(c.par[Q] + ix[Q]);
   double v0, v1;
@@ -200,17 +214,27 @@ __device__ __forceinline__ double interp_axis(const GrCloudyDev &c, const double
   return (in[Q] - x0) * slope + v0;
 }
 
-// (force-inlined on purpose: a real call would take the address of a member of the kernel's
-// by-value parameter copy, which sends the whole copy - and with it every instantiation of
-// the solve kernel, including the ones where this code is dead - to local memory: the compact
-// solve kernel ran 2.15x slower with a 1952-byte stack frame)
 template <int R>
-__device__ __forceinline__ double interp_rank(const GrCloudyDev &c, const double *data, const double (&in)[R])
+__device__ __noinline__ double interp_rank(const InterpAxes c, const double *data, double in0, double in1,
+                                           double in2, double in3, double in4)
 {
+  const double all[5] = {in0, in1, in2, in3, in4};
+  double in[R];
   long long ix[R];
 #pragma unroll
-  for (int q = 0; q < R; q++) ix[q] = axis_index(in[q], c.par[q], c.dpar[q], c.dim[q]);
+  for (int q = 0; q < R; q++) {
+    in[q] = all[q];
+    ix[q] = axis_index(in[q], c.par[q], c.dpar[q], c.dim[q]);
+  }
   return interp_axis<R, 0>(c, data, in, ix, 0);
+}
+
+__device__ __forceinline__ InterpAxes interp_axes_of(const GrCloudyDev &c)
+{
+  InterpAxes a;
+#pragma unroll
+  for (int q = 0; q < 5; q++) { a.par[q] = c.par[q]; a.dim[q] = c.dim[q]; a.dpar[q] = c.dpar[q]; }
+  return a;
 }
 
 // ---- old-style tables, any rank 1..5 (cool1d_cloudy_old_tables_g.F:4-335).  Rank 4 adds the
@@ -224,7 +248,8 @@ __device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c
   double log_n_h = 0.0, log_Z = 0.0, log_e_frac = 0.0, cl_e_frac = 1.0;
   if (c.rank > 1) log_n_h = DLOG10(rhoH * P.dom);
   if (c.rank > 2) log_Z = DLOG10(metallicity);
-  if (c.rank > 3) {                              // :138-146
+  const bool rank45 = (P.iold45 != 0) && c.rank > 3;   // compiled only into the VAR_RANK45 instantiations
+  if (rank45) {                                  // :138-146
     const double fh = rhoH / d;
     const double e_frac = 2.0 * de / (d * (1.0 + fh));
     log_e_frac = dmin(log10(e_frac), 0.0);       // e_frac = 0 must give -Inf: library log10
@@ -233,19 +258,15 @@ __device__ inline double cloudy_old_edot(const GrParams &P, const GrCloudyDev &c
   auto look = [&](const double *data, double lt) {
     if (c.rank == 1) return interp1(c, data, lt);
     if (c.rank == 2) return interp2(c, data, log_n_h, lt);
-    if (c.rank == 3) return interp3(c, data, log_n_h, log_Z, lt);
-    if (c.rank == 4) {
-      const double in[4] = {log_n_h, log_Z, log_e_frac, lt};
-      return interp_rank<4>(c, data, in);
-    }
-    const double in[5] = {log_n_h, log_Z, log_e_frac, P.zr, lt};
-    return interp_rank<5>(c, data, in);
+    if (c.rank == 3 || !rank45) return interp3(c, data, log_n_h, log_Z, lt);
+    if (c.rank == 4) return interp_rank<4>(interp_axes_of(c), data, log_n_h, log_Z, log_e_frac, lt, 0.0);
+    return interp_rank<5>(interp_axes_of(c), data, log_n_h, log_Z, log_e_frac, P.zr, lt);
   };
   double edot_met = -DEXP10(look(c.cooling, log10tem));
   if (P.icmbTfloor == 1 && (log10tem - log10_tCMB) < 2.0)
     edot_met = edot_met + DEXP10(look(c.cooling, log10_tCMB));
   if (P.iClHeat == 1) edot_met = edot_met + DEXP10(look(c.heating, log10tem));
-  if (c.rank > 3) edot_met = edot_met * cl_e_frac;
+  if (rank45) edot_met = edot_met * cl_e_frac;
   return edot_met * rhoH * d;
 }
 
