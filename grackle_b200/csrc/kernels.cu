@@ -364,6 +364,12 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 #ifndef GRB_GROUP_WARPS_LEAN_SMALL
 #define GRB_GROUP_WARPS_LEAN_SMALL 1
 #endif
+// ... and the general / dust + shielding kernels of the H2 networks (pc = 2, 3: the most code per
+// subcycle) with 8 (general C3 +9 %, C4 +4 %, dust + shielding C3 +1.5 % over 4; pc = 0/1 -2 / -10 %)
+#ifndef GRB_GROUP_WARPS_BIG
+#define GRB_GROUP_WARPS_BIG 8
+#endif
+static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS_BIG) == 0, "CTA must be whole lockstep groups");
 // lanes per cell in the cooperative table fetches (fewer lanes = more loads per lane and pass)
 #ifndef GRB_G_MAIN
 #define GRB_G_MAIN 8
@@ -733,7 +739,9 @@ __global__ void __launch_bounds__(GRB_SOLVE_THREADS, GRB_SOLVE_MINBLOCKS) k_solv
   GrParams P = P0;
   P.fm_tab = fm;
   variant_flags<VAR>(P);
-  solve_cells<PC, PIPE, (VAR != VAR_LEAN) ? GRB_GROUP_WARPS : (PC <= 1) ? GRB_GROUP_WARPS_LEAN_SMALL : GRB_GROUP_WARPS_LEAN>(P);
+  solve_cells<PC, PIPE,
+              (VAR != VAR_LEAN) ? ((PC <= 1) ? GRB_GROUP_WARPS : GRB_GROUP_WARPS_BIG)
+                                : ((PC <= 1) ? GRB_GROUP_WARPS_LEAN_SMALL : GRB_GROUP_WARPS_LEAN)>(P);
 }
 
 // ------------------------------------------------------------------------------
