@@ -443,7 +443,9 @@ __device__ __forceinline__ void coop_fetch(const double *table, int my_off, doub
 // log-T bin, warp-cooperative coalesced fetch of the cooling-table row into shared-memory
 // slots (per-thread gathers kept the L1 at ~3/4 of its wavefront rate), log/exp table in
 // shared memory.  VAR: optional physics modules folded away at compile time, as for k_solve.
+#ifndef GRB_CT_THREADS
 #define GRB_CT_THREADS 128
+#endif
 #define GRB_CT_STRIDE 25
 template <int PC, int VAR>
 __global__ void __launch_bounds__(GRB_CT_THREADS) k_cooling_time(const __grid_constant__ GrParams P0)
@@ -804,13 +806,13 @@ void grb_launch_temperature_table(const GrParams &P, cudaStream_t st)
 
 void grb_launch_cooling_time(const GrParams &P, cudaStream_t st)
 {
-  const unsigned nb = blocks_for(P.nactive, 128);
+  const unsigned nb = blocks_for(P.nactive, GRB_CT_THREADS);
   const int var = grb_solve_variant_for(P);
 #define CALL(PCV)                                                                      \
-  if (var == VAR_LEAN) k_cooling_time<PCV, VAR_LEAN><<<nb, 128, 0, st>>>(P);           \
-  else if (var == VAR_DUST_SHIELD) k_cooling_time<PCV, VAR_DUST_SHIELD><<<nb, 128, 0, st>>>(P); \
-  else if (var == VAR_RANK45) k_cooling_time<PCV, VAR_RANK45><<<nb, 128, 0, st>>>(P);            \
-  else k_cooling_time<PCV, VAR_GENERAL><<<nb, 128, 0, st>>>(P);
+  if (var == VAR_LEAN) k_cooling_time<PCV, VAR_LEAN><<<nb, GRB_CT_THREADS, 0, st>>>(P);           \
+  else if (var == VAR_DUST_SHIELD) k_cooling_time<PCV, VAR_DUST_SHIELD><<<nb, GRB_CT_THREADS, 0, st>>>(P); \
+  else if (var == VAR_RANK45) k_cooling_time<PCV, VAR_RANK45><<<nb, GRB_CT_THREADS, 0, st>>>(P);            \
+  else k_cooling_time<PCV, VAR_GENERAL><<<nb, GRB_CT_THREADS, 0, st>>>(P);
   DISPATCH_PC(P.ispecies, CALL)
 #undef CALL
 }
