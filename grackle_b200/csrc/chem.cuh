@@ -71,12 +71,15 @@ __device__ __forceinline__ TIndex t_index(const GrParams &P, double logtem)
 //                 calculate_* kernels, shared-memory slots in the solve kernel).
 // `first` = (iter == 1).  tgasold is the per-cell carry between subcycles.
 // ---------------------------------------------------------------------------------
-template <int PC>
+// SET_Z = false: the caller has already put the cell's metallicity into th (the solve kernel
+// forms it once per cell, not once per subcycle: metal and total density do not change)
+template <int PC, bool SET_Z = true>
 __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool first, double &tgasold,
                                      Thermo &th, bool lookup_follows)
 {
   th.p2d = (P.gamma - 1.0) * c.d * c.e;
-  th.tdust = 0.0; th.metallicity = 0.0; th.dust2gas = 0.0;
+  th.tdust = 0.0; th.dust2gas = 0.0;
+  if (SET_Z) th.metallicity = 0.0;
 
   if (PC == 0) {
     th.rhoH = (P.imetal == 1) ? P.fh * (c.d - c.metal) : P.fh * c.d;
@@ -114,13 +117,22 @@ __device__ inline double thermo_head(const GrParams &P, const Cell &c, bool firs
     }
   }
 
-  if (P.imetal == 1) th.metallicity = ddiv(c.metal, c.d) * P.inv_zsolar;
+  if (SET_Z && P.imetal == 1) th.metallicity = ddiv(c.metal, c.d) * P.inv_zsolar;
   if (first) tgasold = th.tgas;
 
-  // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211)
-  th.logtgas = (PC > 0 && lookup_follows) ? DLOG(th.tgas) : 0.0;
-
-  double logtem = DLOG(0.5 * (th.tgas + tgasold));
+  // ln(tgas) for the rate lookup that follows in the solve (lookup_cool_rates1d_g :1211) and the
+  // logarithm the cooling tables are read at: two independent evaluations, one basic block
+  double logtem;
+  {
+    const double tmean = 0.5 * (th.tgas + tgasold);
+    FmFast f{P.fm_tab, false};
+    th.logtgas = (PC > 0 && lookup_follows) ? f.log(th.tgas) : 0.0;
+    logtem = f.log(tmean);
+    if (f.bad) {
+      th.logtgas = (PC > 0 && lookup_follows) ? DLOG(th.tgas) : 0.0;
+      logtem = DLOG(tmean);
+    }
+  }
   logtem = dmax(logtem, P.logtem0);
   logtem = dmin(logtem, P.logtem9);
   return logtem;
@@ -172,7 +184,13 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     }
     const double galdl = gaHI * c.HI + gaH2 * c.H2I / 2.0 + gaHe * c.HeI / 4.0 + gaHp * c.HII + gael * c.de;
     const double gphdl1 = h2lte * dom_inv;
-    edot = edot - ddiv_s((double)P.ih2co * fudge * c.H2I * h2lte, 1.0 + ddiv_s(gphdl1, galdl)) * (0.5 * dom_inv);
+    {
+      const double num = (double)P.ih2co * fudge * c.H2I * h2lte;
+      FmFast f{P.fm_tab, false};
+      double q = f.div_s(num, 1.0 + f.div_s(gphdl1, galdl));
+      if (f.bad) q = ddiv_s(num, 1.0 + ddiv_s(gphdl1, galdl));
+      edot = edot - q * (0.5 * dom_inv);
+    }
     if (P.iciecool == 1 && c.d * dom > 1e10) {
       const double cieco = cv(L_CIECO);
       double tau = POW_POS((c.d / 2e16) * dom, 2.8);

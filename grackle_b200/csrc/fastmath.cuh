@@ -25,6 +25,7 @@
 
 #ifdef __CUDACC__
 #define GRB_FM_HD __device__ __forceinline__
+#define GRB_FM_MEM __device__ __forceinline__
 #define GRB_FM_CONST static __constant__
 #ifdef GRB_FM_NOINLINE
 #define GRB_FM_FN __device__ __noinline__      /* dlog / dexp / dexp10 as subroutines (code size experiment) */
@@ -33,6 +34,7 @@
 #endif
 #else
 #define GRB_FM_HD static inline
+#define GRB_FM_MEM inline
 #define GRB_FM_FN static inline
 #define GRB_FM_CONST static const
 #endif
@@ -100,29 +102,41 @@ static inline double fm_exp_slow(double x) { return exp(x); }
 static inline double fm_exp10_slow(double x) { return pow(10.0, x); }
 #endif
 
-// 1/b for finite normal b with 1/b representable: seed + two Newton steps
+// 1/b for finite normal b with 1/b representable: r0 (1 + e)(1 + e^2), e = 1 - b r0 (see ddiv)
 GRB_FM_HD double drcp(double b)
 {
-  double r = fm_rcp_seed(b);
-  double e = fma(-b, r, 1.0);
-  r = fma(r, e, r);
-  e = fma(-b, r, 1.0);
-  return fma(r, e, r);
+  const double r0 = fm_rcp_seed(b);
+  const double e = fma(-b, r0, 1.0);
+  const double r1 = fma(r0, e, r0);
+  const double e2 = e * e;
+  return fma(r1, e2, r1);
 }
 
-// a/b under the same conditions.  One Newton step takes the seed's relative error d0 ~ 2^-20
-// to d = 2^-40; the residual correction q' = q + r (a - b q) then leaves a/b (1 - d^2): full
-// precision without the second Newton step.  NOT for denominators that can be zero or
-// non-finite: the result would be NaN, not Inf - use ddiv_s.
+// a/b under the same conditions, as a short dependency chain: with e = 1 - b r0 (|e| ~ 2^-20 for
+// the hardware seed r0) 1/b = r0 (1 + e + e^2 + e^3 + ...), and
+//     q = a r0 (1 + e)(1 + e^2)
+// is a/b (1 - e^4): full precision from three dependent FMA-class steps (e -> q1 -> q) with q0 = a r0
+// and e^2 formed beside them, where Newton + residual correction needs five in a row.  The kernel
+// holds four warps per scheduler, so the length of such chains is what it waits on.  Result within
+// 1.5 ulp (three roundings).  NOT for denominators that can be zero or non-finite: the result
+// would be NaN, not Inf - use ddiv_s.
 GRB_FM_HD double ddiv(double a, double b)
 {
 #ifdef GRB_DDIV_IEEE
   return a / b;
 #endif
+#ifdef GRB_DDIV_NEWTON      /* round 1's form: Newton step + residual correction, five dependent steps */
   double r = fm_rcp_seed(b);
   r = fma(r, fma(-b, r, 1.0), r);
   const double q = a * r;
   return fma(fma(-b, q, a), r, q);
+#endif
+  const double r0 = fm_rcp_seed(b);
+  const double e = fma(-b, r0, 1.0);
+  const double q0 = a * r0;
+  const double q1 = fma(q0, e, q0);
+  const double e2 = e * e;
+  return fma(q1, e2, q1);
 }
 
 // a/b for ANY b: zero, subnormal, Inf and NaN denominators take the IEEE division (a/0 = Inf is
@@ -243,43 +257,50 @@ static inline void fm_fill_tables(double *tab)
 
 GRB_FM_HD double fm_ldtab(const double *p) { return *p; }
 
-GRB_FM_HD double dlog(double x, const double *tab)
+// arguments the lean versions do not handle (they go to the CUDA library function instead)
+GRB_FM_HD bool fm_log_special(double x) { return (unsigned)(fm_hi(x) - 0x00100000) >= 0x7fe00000u; }   // <= 0, subnormal, Inf, NaN
+GRB_FM_HD bool fm_exp_special(double x) { return (fm_hi(x) & 0x7fffffff) > 0x4085e000; }               // |x| > 700, Inf, NaN
+GRB_FM_HD bool fm_exp10_special(double x) { return (fm_hi(x) & 0x7fffffff) > 0x4072c000; }             // |x| > 300, Inf, NaN
+GRB_FM_HD bool fm_den_special(double b) { return (unsigned)((fm_hi(b) & 0x7ff00000) - 0x00100000) >= 0x7fe00000u; }
+
+// The unchecked cores.  Polynomials in Estrin form: the degree-4 / degree-3 tails are two
+// dependent steps deep instead of four / three (same coefficients, ~2 ulp as before).
+GRB_FM_HD double dlog_nc(double x, const double *tab)
 {
   const int hi = fm_hi(x);
-  if ((unsigned)(hi - 0x00100000) >= 0x7fe00000u) return fm_log_slow(x);   // <= 0, subnormal, Inf, NaN
   const int i = (hi >> 13) & 0x7f;
   const double m = fm_make((hi & 0x000fffff) | 0x3ff00000, fm_lo(x));     // [1, 2)
   const double inv = fm_ldtab(tab + 2 * i), lc = fm_ldtab(tab + 2 * i + 1);
   const double r = fma(m, inv, -1.0);
   const double de = (double)((hi >> 20) - 1023);
   const double big = fma(de, FM_K[0], lc);
-  double p = FM_T[4];
-  p = fma(p, r, FM_T[3]);
-  p = fma(p, r, FM_T[2]);
-  p = fma(p, r, FM_T[1]);
-  p = fma(p, r, FM_T[0]);
-  const double sm = fma(r * r, p, r);                     // log1p(r)
+  // log1p(r) = r + r^2 (c0 + c1 r + c2 r^2 + c3 r^3 + c4 r^4)
+  const double r2 = r * r;
+  const double t01 = fma(FM_T[1], r, FM_T[0]);
+  const double t23 = fma(FM_T[3], r, FM_T[2]);
+  const double r4 = r2 * r2;
+  const double u = fma(t23, r2, t01);
+  const double p = fma(FM_T[4], r4, u);
+  const double sm = fma(r2, p, r);
   return big + fma(de, FM_K[1], sm);
 }
-
-GRB_FM_HD double dlog10(double x, const double *tab) { return dlog(x, tab) * FM_K[9]; }
 
 // 2^n * T * exp(r), |r| <= ln2/128
 GRB_FM_HD double fm_exp_tab_core(double r, int kk, const double *tab)
 {
   const double T = fm_ldtab(tab + 256 + (kk & 63));
-  double p = FM_T[8];
-  p = fma(p, r, FM_T[7]);
-  p = fma(p, r, FM_T[6]);
-  p = fma(p, r, FM_T[5]);
-  const double em1 = fma(r * r, p, r);                    // exp(r) - 1
+  // exp(r) - 1 = r + r^2 (c5 + c6 r + c7 r^2 + c8 r^3)
+  const double r2 = r * r;
+  const double t0 = fma(FM_T[6], r, FM_T[5]);
+  const double t1 = fma(FM_T[8], r, FM_T[7]);
+  const double p = fma(t1, r2, t0);
+  const double em1 = fma(r2, p, r);
   const double v = fma(T, em1, T);
   return fm_make(fm_hi(v) + ((kk >> 6) << 20), fm_lo(v));
 }
 
-GRB_FM_HD double dexp(double x, const double *tab)
+GRB_FM_HD double dexp_nc(double x, const double *tab)
 {
-  if ((fm_hi(x) & 0x7fffffff) > 0x4085e000) return fm_exp_slow(x);        // |x| > 700, Inf, NaN
   const double t = fma(x, FM_T[9], FM_K[3]);
   const int kk = fm_lo(t);
   const double nf = t - FM_K[3];
@@ -288,9 +309,8 @@ GRB_FM_HD double dexp(double x, const double *tab)
   return fm_exp_tab_core(r, kk, tab);
 }
 
-GRB_FM_HD double dexp10(double x, const double *tab)
+GRB_FM_HD double dexp10_nc(double x, const double *tab)
 {
-  if ((fm_hi(x) & 0x7fffffff) > 0x4072c000) return fm_exp10_slow(x);      // |x| > 300, Inf, NaN
   const double t = fma(x, FM_T[12], FM_K[3]);
   const int kk = fm_lo(t);
   const double nf = t - FM_K[3];
@@ -299,6 +319,43 @@ GRB_FM_HD double dexp10(double x, const double *tab)
   const double y = fma(r, FM_K[8], r * FM_K[7]);
   return fm_exp_tab_core(y, kk, tab);
 }
+
+// the checked forms: one rarely taken branch per call
+GRB_FM_HD double dlog(double x, const double *tab) { return fm_log_special(x) ? fm_log_slow(x) : dlog_nc(x, tab); }
+GRB_FM_HD double dlog10(double x, const double *tab) { return dlog(x, tab) * FM_K[9]; }
+GRB_FM_HD double dexp(double x, const double *tab) { return fm_exp_special(x) ? fm_exp_slow(x) : dexp_nc(x, tab); }
+GRB_FM_HD double dexp10(double x, const double *tab) { return fm_exp10_special(x) ? fm_exp10_slow(x) : dexp10_nc(x, tab); }
+
+// ---------------------------------------------------------------------------------------
+// Math policies.  A stretch of per-cell physics with several independent elementary-function
+// calls is written once against a policy `m` (m.log, m.exp, m.exp10, m.pow, m.div_s ...) and run
+//   1. with FmFast: every call is the unchecked core, and the "this argument needs the library
+//      function" tests are OR-ed into one flag - no branch per call, so the whole stretch is one
+//      basic block in which the compiler interleaves the independent polynomial / Newton
+//      chains (with a branch around every call each chain ran alone: `wait` was the kernel's
+//      second largest stall reason);
+//   2. only if the flag came up, once more with FmChecked (the per-call checked forms above),
+//      whose results are exactly what the code produced before.
+// ---------------------------------------------------------------------------------------
+struct FmFast {
+  const double *tab;
+  bool bad;
+  GRB_FM_MEM double log(double x) { bad |= fm_log_special(x); return dlog_nc(x, tab); }
+  GRB_FM_MEM double log10(double x) { return log(x) * FM_K[9]; }
+  GRB_FM_MEM double exp(double x) { bad |= fm_exp_special(x); return dexp_nc(x, tab); }
+  GRB_FM_MEM double exp10(double x) { bad |= fm_exp10_special(x); return dexp10_nc(x, tab); }
+  GRB_FM_MEM double pow(double x, double y) { return exp(y * log(x)); }
+  GRB_FM_MEM double div_s(double a, double b) { bad |= fm_den_special(b); return ddiv(a, b); }
+};
+struct FmChecked {
+  const double *tab;
+  GRB_FM_MEM double log(double x) { return dlog(x, tab); }
+  GRB_FM_MEM double log10(double x) { return dlog10(x, tab); }
+  GRB_FM_MEM double exp(double x) { return dexp(x, tab); }
+  GRB_FM_MEM double exp10(double x) { return dexp10(x, tab); }
+  GRB_FM_MEM double pow(double x, double y) { return dexp(y * dlog(x, tab), tab); }
+  GRB_FM_MEM double div_s(double a, double b) { return ddiv_s(a, b); }
+};
 
 GRB_FM_HD double dpow_pos(double x, double y, const double *tab) { return dexp(y * dlog(x, tab), tab); }
 

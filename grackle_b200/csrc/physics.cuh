@@ -133,12 +133,12 @@ __device__ inline double cloudy_lookup(const GrCloudyDev &c, const double *data,
 //     multiplications with its inverse (the grids are uniform; the difference to the stored
 //     axis values is one rounding, ~1e-16),
 //   * the CMB-floor term (cooling at T_CMB, cell-invariant along T) read from a per-row array.
-__device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCloudyDev &c, double rhoH,
-                                                   double metallicity, double logtem, int icmbTfloor,
-                                                   int iZscale)
+template <class M>
+__device__ __forceinline__ double cloudy_edot_fast_m(M &m, const GrParams &P, const GrCloudyDev &c, double rhoH,
+                                                     double metallicity, double logtem, int icmbTfloor, int iZscale)
 {
   const double log10tem = logtem * GRB_INV_LN10;
-  const double log_n_h = DLOG10(rhoH * P.dom);
+  const double log_n_h = m.log10(rhoH * P.dom);
   int i1 = (int)((log_n_h - c.par0[0]) * c.inv_dpar[0]) + 1;
   i1 = min(c.fdim[0] - 1, max(1, i1));
   int i2 = (int)((log10tem - c.par0[1]) * c.inv_dpar[1]) + 1;
@@ -151,14 +151,29 @@ __device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCl
   double m0 = 0.0, m1 = 0.0;
   if (floor_on) { m0 = ld(c.cmb + i1 - 1); m1 = ld(c.cmb + i1); }
   const double c0 = w2 * (v01.x - v00.x) + v00.x, c1 = w2 * (v11.x - v10.x) + v10.x;
-  double edot_met = -DEXP10(w1 * (c1 - c0) + c0);
-  if (floor_on) edot_met = edot_met + DEXP10(w1 * (m1 - m0) + m0);
-  if (c.get_heat == 1) {
-    const double h0 = w2 * (v01.y - v00.y) + v00.y, h1 = w2 * (v11.y - v10.y) + v10.y;
-    edot_met = edot_met + DEXP10(w1 * (h1 - h0) + h0);
-  }
+  // the (up to) three powers of ten are independent of each other: formed side by side
+  const double e_cool = m.exp10(w1 * (c1 - c0) + c0);
+  const double e_floor = m.exp10(w1 * (m1 - m0) + m0);
+  const double h0 = w2 * (v01.y - v00.y) + v00.y, h1 = w2 * (v11.y - v10.y) + v10.y;
+  const double e_heat = m.exp10(w1 * (h1 - h0) + h0);
+  double edot_met = -e_cool;
+  if (floor_on) edot_met = edot_met + e_floor;
+  if (c.get_heat == 1) edot_met = edot_met + e_heat;
   if (iZscale == 1) edot_met = edot_met * metallicity;
   return edot_met * rhoH * rhoH;
+}
+
+__device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCloudyDev &c, double rhoH,
+                                                   double metallicity, double logtem, int icmbTfloor,
+                                                   int iZscale)
+{
+  FmFast f{P.fm_tab, false};
+  double v = cloudy_edot_fast_m(f, P, c, rhoH, metallicity, logtem, icmbTfloor, iZscale);
+  if (f.bad) {       // an argument outside the lean functions' range: once more with the checked forms
+    FmChecked e{P.fm_tab};
+    v = cloudy_edot_fast_m(e, P, c, rhoH, metallicity, logtem, icmbTfloor, iZscale);
+  }
+  return v;
 }
 
 __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, double rhoH,

@@ -25,7 +25,7 @@ __global__ void k_check(double *worst, unsigned long long *bad, const double *ta
     const double e2 = rel(grb::ddiv(-a, b), -a / b);
     const double e3 = rel(grb::ddiv(a, -b), a / -b);
     const double e = fmax(e1, fmax(e2, e3));
-    if (e > 4e-16) atomicAdd(bad + 0, 1ULL);
+    if (e > 4.5e-16) atomicAdd(bad + 0, 1ULL);
     atomicMax((unsigned long long *)worst + 0, (unsigned long long)__double_as_longlong(e));
   }
   {

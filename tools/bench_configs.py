@@ -19,7 +19,7 @@ if len(sys.argv) > 3 and sys.argv[3] == "general":
     lib.grb200_set_solve_variant(1)      # force the general instantiation
 table = synth_tables.ensure()
 dev = torch.device("cuda", 0)
-for name in ("C1", "C2", "C3", "C4"):
+for name in os.environ.get("CONFIGS", "C1,C2,C3,C4").split(","):
     params, dt, _ = sf.config(name, table)
     pc = params["primordial_chemistry"]
     ch = capi.Chemistry(lib, **params).initialize()
@@ -32,7 +32,7 @@ for name in ("C1", "C2", "C3", "C4"):
         g.set(k, int(v.data_ptr()))
     st = capi.SolveStats()
     ms = []
-    for it in range(3):
+    for it in range(int(os.environ.get("REPS", "3"))):
         for k in work:
             work[k].copy_(pristine[k])
         torch.cuda.synchronize()

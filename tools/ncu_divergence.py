@@ -7,8 +7,12 @@ rep, so, func = sys.argv[1:4]
 ntop = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, check=True, capture_output=True)
-cub = [f for f in os.listdir(tmp) if f.startswith("kernels")][0]
-dis = subprocess.run(["nvdisasm", "-g", os.path.join(tmp, cub)], capture_output=True, text=True).stdout
+dis = ""
+for cub in sorted(os.listdir(tmp)):          # the cubin that holds the kernel (one per translation unit)
+    d = subprocess.run(["nvdisasm", "-g", os.path.join(tmp, cub)], capture_output=True, text=True).stdout
+    if ".text." + func in d:
+        dis = d
+        break
 addr2 = {}; cur = None; inside = False
 for ln in dis.splitlines():
     if ln.startswith(".text."):
