@@ -151,13 +151,13 @@ __device__ __forceinline__ double cloudy_edot_fast_m(M &m, const GrParams &P, co
   double m0 = 0.0, m1 = 0.0;
   if (floor_on) { m0 = ld(c.cmb + i1 - 1); m1 = ld(c.cmb + i1); }
   const double c0 = w2 * (v01.x - v00.x) + v00.x, c1 = w2 * (v11.x - v10.x) + v10.x;
-  // the (up to) three powers of ten are independent of each other: formed side by side
+  // cooling and heating: two independent powers of ten, formed side by side; the CMB-floor term
+  // only where the gas is within two decades of T_CMB (few cells: a branch, not a third power)
   const double e_cool = m.exp10(w1 * (c1 - c0) + c0);
-  const double e_floor = m.exp10(w1 * (m1 - m0) + m0);
   const double h0 = w2 * (v01.y - v00.y) + v00.y, h1 = w2 * (v11.y - v10.y) + v10.y;
-  const double e_heat = m.exp10(w1 * (h1 - h0) + h0);
+  const double e_heat = (c.get_heat == 1) ? m.exp10(w1 * (h1 - h0) + h0) : 0.0;
   double edot_met = -e_cool;
-  if (floor_on) edot_met = edot_met + e_floor;
+  if (floor_on) edot_met = edot_met + m.exp10(w1 * (m1 - m0) + m0);
   if (c.get_heat == 1) edot_met = edot_met + e_heat;
   if (iZscale == 1) edot_met = edot_met * metallicity;
   return edot_met * rhoH * rhoH;

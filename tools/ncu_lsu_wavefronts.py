@@ -24,8 +24,9 @@ for r in rows[2:]:
                      samples=num(r, "# Samples")))
 per = a.per
 if not per:
-    bars = [x["n"] for x in recs if x["op"].startswith("BAR") or x["op"].startswith("B2R")]
-    per = max(bars) if bars else 1.0
+    # executions of the loop body = the most frequent execution count among the kernel's instructions
+    cnt = collections.Counter(x["n"] for x in recs if x["n"] > 0)
+    per = cnt.most_common(1)[0][0] if cnt else 1.0
 tot = sum(x["n"] for x in recs)
 print("instructions per unit: %.1f   (unit count %.0f)" % (tot / per, per))
 print("shared wavefronts per unit: %.1f (ideal %.1f)   global tag requests per unit: %.1f   L2 sectors per unit: %.1f"
