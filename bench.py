@@ -32,6 +32,13 @@ sys.path.insert(0, ROOT)
 
 from grackle_b200 import capi, synth_fields as sf, synth_tables  # noqa: E402
 
+
+def _oracle():
+    """the CPU oracle's loader (test infrastructure, tests/oracle_lib.py): CPU-baseline legs only"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    return oracle_lib
+
 SLAB = (1024, 1024, 128)            # (ni, nj, nk) per GPU
 BYTES_PER_CELL = 224                # SURVEY 8d: 15 fields read + 13 written, FP64
 # FP64 operations per cell-subcycle of the reference algorithm at config C4, COUNTED by the
@@ -114,10 +121,11 @@ def chemistry_params(table):
 def cpu_solve_rate(table, sample_dims, steps, warmup, offset=0):
     """cells/s of the CPU oracle (reference C glue + C++ restatement of its Fortran, OpenMP
     schedule(guided,1) over rows like the reference) on a bounded sample of the workload"""
-    lib = capi.load_oracle()
+    ol = _oracle()
+    lib = ol.load_oracle()
     params, dt = chemistry_params(table)
     cores = os.cpu_count() or 1
-    ch = capi.Chemistry(lib, is_oracle=True, omp_nthreads=cores, **params).initialize()
+    ch = ol.OracleChemistry(lib, omp_nthreads=cores, **params).initialize()
     n = int(np.prod(sample_dims))
     idx = np.arange(offset, offset + n, dtype=np.int64)
     fields = sf.make_fields(idx, 3, params, ch.temperature_units, "B")

@@ -1,11 +1,8 @@
 """ctypes view of Grackle's C ABI (include/grackle.h).
 
-The same binding drives two shared libraries that export the identical ABI:
-
-* the product, ``grackle_b200/lib/libgrackle_b200.so`` (CUDA, sm_100a) - `load_product()`;
-* the test oracle, ``oracle/_ref/libgrackle_oracle.so`` (reference C glue + C++ restatement
-  of the Fortran, CPU) - `load_oracle()`; ONLY tests/, smoke() and bench.py's CPU-baseline
-  legs may call that.
+It binds the product, ``grackle_b200/lib/libgrackle_b200.so`` (CUDA, sm_100a) - `load_product()`.
+(The test oracle exports the identical ABI; its loader lives with the tests, tests/oracle_lib.py,
+and reuses the struct definitions below.)
 
 This module is the Python stand-in for pygrackle's Cython layer
 (src/python/pygrackle/grackle_wrapper.pyx:630-920 in the reference): it fills
@@ -21,7 +18,6 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(_HERE)
 # GRB200_LIB selects another BUILD of the same CUDA library (tuning experiments); never a fallback
 PRODUCT_SO = os.environ.get("GRB200_LIB") or os.path.join(_HERE, "lib", "libgrackle_b200.so")
-ORACLE_SO = os.path.join(REPO, "oracle", "_ref", "libgrackle_oracle.so")
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int)
@@ -182,29 +178,6 @@ def load_product():
     return lib
 
 
-def load_oracle(counting=False):
-    """Load the CPU oracle (tests / smoke / bench CPU-baseline only).  counting=True loads the
-    operation-counting build of the same code (oracle/flopcount.hpp)."""
-    so = ORACLE_SO.replace("libgrackle_oracle.so", "libgrackle_oracle_count.so") if counting else ORACLE_SO
-    if not os.path.exists(so):
-        raise ExtensionMissing("oracle library %s is missing (make -C oracle)" % so)
-    lib = _declare(C.CDLL(so, mode=C.RTLD_LOCAL))
-    if counting:
-        lib.oracle_flop_counts.argtypes = [C.POINTER(C.c_longlong), C.c_int]
-        lib.oracle_flop_counts.restype = None
-    lib.oracle_inject_cloudy.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong),
-                                         C.POINTER(c_dp), c_dp, c_dp, c_dp]
-    lib.oracle_inject_cloudy.restype = None
-    lib.oracle_inject_uvb.argtypes = [C.c_longlong, C.POINTER(c_dp)]
-    lib.oracle_inject_uvb.restype = None
-    lib.oracle_clear_injected.restype = None
-    lib.oracle_last_subcycles_sum.restype = C.c_longlong
-    lib.oracle_set_roundoff_noise.argtypes = [C.c_double, C.c_ulonglong]
-    lib.oracle_set_roundoff_noise.restype = None
-    lib.oracle_last_subcycles_max.restype = C.c_longlong
-    return lib
-
-
 # ---------------------------------------------------------------------------
 # convenience layer: one chemistry object bound to one library
 # ---------------------------------------------------------------------------
@@ -223,9 +196,8 @@ def _dptr(a):
 class Chemistry:
     """chemistry_data + chemistry_data_storage + code_units for one library."""
 
-    def __init__(self, lib, is_oracle=False, **params):
+    def __init__(self, lib, **params):
         self.lib = lib
-        self.is_oracle = is_oracle
         self.chem = ChemistryData()
         lib.set_default_chemistry_parameters(C.byref(self.chem))
         self.chem.omp_nthreads = int(params.pop("omp_nthreads", os.cpu_count() or 1))
@@ -252,8 +224,7 @@ class Chemistry:
 
     def initialize(self):
         self.lib.set_velocity_units(C.byref(self.units))
-        if self.is_oracle:
-            self._inject_tables()
+        self._before_initialize()
         ok = self.lib._initialize_chemistry_data(C.byref(self.chem), C.byref(self.rates),
                                                  C.byref(self.units))
         if ok != 1:
@@ -266,48 +237,8 @@ class Chemistry:
             self.lib._free_chemistry_data(C.byref(self.chem), C.byref(self.rates))
             self.initialized = False
 
-    # oracle only: read the data file in Python and hand the raw arrays over
-    def _inject_tables(self):
-        from . import h5lite
-        self.lib.oracle_clear_injected()
-        need_file = (self.chem.primordial_chemistry == 0 or self.chem.metal_cooling == 1 or
-                     (self.chem.UVbackground == 1 and self.chem.primordial_chemistry > 0))
-        if not need_file:
-            return
-        f = h5lite.read_file(self._file.decode())
-        old_style = 1 if "old_style" in f.attrs else 0
-        keep = self._keep = []
-        for which, group in enumerate(("Primordial", "Metals")):
-            path = "CoolingRates/%s/Cooling" % group
-            if path not in f:
-                continue
-            node = f[path]
-            rank = int(node.attrs["Rank"])
-            dims = np.atleast_1d(node.attrs["Dimension"]).astype(np.int64)
-            pars = []
-            for q in range(rank):
-                name = "Temperature" if q == rank - 1 else "Parameter%d" % (q + 1)
-                pars.append(np.ascontiguousarray(node.attrs[name], dtype=np.float64))
-            cool = np.ascontiguousarray(node.data, dtype=np.float64).ravel()
-            hpath, mpath = "CoolingRates/%s/Heating" % group, "CoolingRates/%s/MMW" % group
-            heat = np.ascontiguousarray(f[hpath].data, dtype=np.float64).ravel() if hpath in f else None
-            mmw = np.ascontiguousarray(f[mpath].data, dtype=np.float64).ravel() if mpath in f else None
-            parr = (c_dp * rank)(*[_dptr(p) for p in pars])
-            darr = (C.c_longlong * rank)(*[int(d) for d in dims])
-            keep += [pars, cool, heat, mmw]
-            self.lib.oracle_inject_cloudy(which, old_style, rank, darr, parr, _dptr(cool), _dptr(heat), _dptr(mmw))
-        if "UVBRates/z" in f:
-            names = ["z", "Chemistry/k24", "Chemistry/k25", "Chemistry/k26", "Chemistry/k27",
-                     "Chemistry/k28", "Chemistry/k29", "Chemistry/k30", "Chemistry/k31",
-                     "Photoheating/piHI", "Photoheating/piHeI", "Photoheating/piHeII",
-                     "CrossSections/hi_avg_crs", "CrossSections/hei_avg_crs", "CrossSections/heii_avg_crs"]
-            vecs = []
-            for n in names:
-                p = "UVBRates/" + n
-                vecs.append(np.ascontiguousarray(f[p].data, dtype=np.float64).ravel() if p in f else None)
-            keep.append(vecs)
-            varr = (c_dp * 15)(*[_dptr(v) for v in vecs])
-            self.lib.oracle_inject_uvb(len(vecs[0]), varr)
+    def _before_initialize(self):
+        """hook for subclasses (the tests' oracle binding hands its table arrays over here)"""
 
     @property
     def temperature_units(self):

@@ -14,8 +14,15 @@ def pytest_configure(config):
 
 @pytest.fixture(scope="session")
 def oracle_lib():
-    from grackle_b200 import capi
-    return capi.load_oracle()
+    import oracle_lib
+    return oracle_lib.load_oracle()
+
+
+@pytest.fixture(scope="session")
+def oracle_fma_lib():
+    """the reference sources rebuilt with floating-point contraction on (oracle/Makefile)"""
+    import oracle_lib
+    return oracle_lib.load_oracle("fma")
 
 
 @pytest.fixture(scope="session")

@@ -18,6 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import parity  # noqa: E402
+import oracle_lib as ol  # noqa: E402
 from grackle_b200 import capi, synth_fields as sf, synth_tables  # noqa: E402
 
 KINDS = ["add_sub", "mul", "div", "compare", "log", "exp", "pow", "sqrt", "other"]
@@ -31,15 +32,15 @@ def counts(lib, reset=True):
 
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
-    cnt = capi.load_oracle(counting=True)
-    ref = capi.load_oracle()
+    cnt = ol.load_oracle("count")
+    ref = ol.load_oracle()
     table = synth_tables.ensure()
     out = {"cells": n, "input_set": "B", "note": "one flop per add/sub/mul/div/compare and per elementary-function call; "
            "max/min count as one compare; sign flips and abs are free; table/field loads are not counted"}
     for name in ("C1", "C2", "C3", "C4"):
         params, dt, _ = sf.config(name, table)
-        cc = capi.Chemistry(cnt, is_oracle=True, omp_nthreads=1, **params).initialize()
-        cr = capi.Chemistry(ref, is_oracle=True, omp_nthreads=1, **params).initialize()
+        cc = ol.OracleChemistry(cnt, omp_nthreads=1, **params).initialize()
+        cr = ol.OracleChemistry(ref, omp_nthreads=1, **params).initialize()
         fields, dt = parity.config_inputs(name, table, n, "B", cr)
         dims = [1, n]      # one cell per row: the reference works row-at-a-time with masks, and finished
                            # cells of a longer row would still be charged the row-level comparisons

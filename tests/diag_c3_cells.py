@@ -14,6 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import parity  # noqa: E402
+import oracle_lib as ol  # noqa: E402
 from grackle_b200 import capi, synth_fields as sf, synth_tables  # noqa: E402
 
 out = open(os.path.join(ROOT, "gpurun_out", "diag_c3.txt"), "w")
@@ -27,7 +28,7 @@ def pr(*a):
 
 n = 1 << 18
 dims = [256, n // 256]
-P, O = capi.load_product(), capi.load_oracle()
+P, O = capi.load_product(), ol.load_oracle()
 table = synth_tables.ensure()
 params, dt, _ = sf.config("C3", table)
 cp, co = parity.make_pair(P, O, params)

@@ -1,11 +1,12 @@
 import sys, os; sys.path.insert(0,"."); sys.path.insert(0,"tests")
 import numpy as np, ctypes as C
 import parity
+import oracle_lib as ol  # noqa: E402
 from grackle_b200 import capi, synth_tables, synth_fields as sf
 out=open("gpurun_out/diag.txt","w")
 def pr(*a):
     print(*a, file=out); out.flush()
-P=capi.load_product(); O=capi.load_oracle(); table=synth_tables.ensure()
+P=capi.load_product(); O=ol.load_oracle(); table=synth_tables.ensure()
 for name,setn in (("C2","H"),("C1","B"),("C4","B"),("C2","B")):
     params, dt, _ = sf.config(name, table)
     cp, co = parity.make_pair(P,O,params)

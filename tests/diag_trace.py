@@ -4,12 +4,13 @@ that many subcycles) and print the per-field relative difference after each coun
 import sys, os; sys.path.insert(0, "."); sys.path.insert(0, "tests")
 import numpy as np, ctypes as C
 import parity
+import oracle_lib as ol  # noqa: E402
 from grackle_b200 import capi, synth_tables, synth_fields as sf
 name, setn = sys.argv[1], sys.argv[2]
 n = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
 ncell = int(sys.argv[4]) if len(sys.argv) > 4 else 2
 trace = len(sys.argv) > 5
-P = capi.load_product(); O = capi.load_oracle(); table = synth_tables.ensure()
+P = capi.load_product(); O = ol.load_oracle(); table = synth_tables.ensure()
 params, dt, _ = sf.config(name, table)
 cp, co = parity.make_pair(P, O, params)
 fields, dt = parity.config_inputs(name, table, n, setn, co)

@@ -7,12 +7,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np
 import parity, test_gpu_variants as tv
+import oracle_lib as ol  # noqa: E402
 from grackle_b200 import capi, synth_tables, synth_fields as sf
 
 out = open(os.path.join(ROOT, "gpurun_out", "diag_variant.txt"), "w")
 def pr(*a):
     print(*a, file=out); out.flush(); print(*a)
-P = capi.load_product(); O = capi.load_oracle(); table = synth_tables.ensure()
+P = capi.load_product(); O = ol.load_oracle(); table = synth_tables.ensure()
 for vid in sys.argv[1:]:
     _, base, over, extras, dustfield = [v for v in tv.VARIANTS if v[0] == vid][0]
     params, dt, _ = sf.config(base, table)

@@ -12,6 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import parity  # noqa: E402
+import oracle_lib as ol  # noqa: E402
 from grackle_b200 import capi, synth_fields as sf, synth_tables  # noqa: E402
 
 
@@ -29,7 +30,7 @@ def main():
         print(*a, file=out)
         out.flush()
 
-    P, O = capi.load_product(), capi.load_oracle()
+    P, O = capi.load_product(), ol.load_oracle()
     table = synth_tables.ensure()
     dims = [256, n // 256]
     pr("# product (CUDA, B200) vs oracle (CPU restatement behind the reference's C glue), %d cells per case" % n)

@@ -19,6 +19,7 @@ import numpy as np
 import pytest
 
 from grackle_b200 import capi, synth_fields as sf
+import oracle_lib as ol  # noqa: E402
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 INCLUDE = os.path.join(ROOT, "include")
@@ -146,7 +147,7 @@ def test_host_tables_bit_identical_to_reference(product_lib, oracle_lib, synth_t
     h5lite.cpp) against the reference's initialize_rates.c / rate_functions.c and its
     post-processing of the data file"""
     params, dt, _ = sf.config(name, synth_table)
-    cp, co = capi.Chemistry(product_lib, **params).initialize(), capi.Chemistry(oracle_lib, is_oracle=True, **params).initialize()
+    cp, co = capi.Chemistry(product_lib, **params).initialize(), ol.OracleChemistry(oracle_lib, **params).initialize()
     try:
         if params["primordial_chemistry"] > 0:
             for t in capi.RATE_TABLE_NAMES:
@@ -196,7 +197,7 @@ def test_host_tables_bit_identical_to_reference(product_lib, oracle_lib, synth_t
 def test_old_style_table_loader(product_lib, oracle_lib, metal_table_2008):
     import freefall_replay as fr
     p = fr.freefall_params(True, metal_table_2008)
-    cp, co = capi.Chemistry(product_lib, **p).initialize(), capi.Chemistry(oracle_lib, is_oracle=True, **p).initialize()
+    cp, co = capi.Chemistry(product_lib, **p).initialize(), ol.OracleChemistry(oracle_lib, **p).initialize()
     assert cp.rates.cloudy_data_new == 0 and co.rates.cloudy_data_new == 0
     a, b = cp.rates.cloudy_metal, co.rates.cloudy_metal
     assert [a.grid_dimension[q] for q in range(3)] == [37, 29, 71] == [b.grid_dimension[q] for q in range(3)]

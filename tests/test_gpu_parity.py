@@ -178,7 +178,7 @@ def test_fastmath_on_device():
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0, out.stdout + out.stderr
     rows = {ln.split()[0]: ln.split()[1:] for ln in out.stdout.strip().splitlines()}
-    assert float(rows["div"][0]) <= 2.3e-16 and float(rows["rcp"][0]) <= 2.3e-16
+    assert float(rows["div"][0]) <= 3.5e-16 and float(rows["rcp"][0]) <= 2.3e-16      # div: <= 1.6 ulp (fastmath.cuh)
     for name in ("log", "exp", "exp10", "tlog", "texp", "texp10"):
         assert float(rows[name][0]) <= 1e-15, (name, rows[name])
 

@@ -8,6 +8,8 @@ import sys
 import numpy as np
 import pytest
 
+import oracle_lib as ol
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DIMS = [8, 4, 7]     # nk = 7 is not divisible by 2: exercises the uneven split
 
@@ -23,13 +25,14 @@ def _worker(rank, world, port, out_dir):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch.distributed as dist
     import parity
+    import oracle_lib as ol
     from grackle_b200 import capi, slabs, synth_fields as sf, synth_tables
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    lib = capi.load_oracle()
+    lib = ol.load_oracle()
     table = synth_tables.ensure()
     params, dt, _ = sf.config("C4", table)
-    ch = capi.Chemistry(lib, is_oracle=True, omp_nthreads=1, **params).initialize()
+    ch = ol.OracleChemistry(lib, omp_nthreads=1, **params).initialize()
     n = int(np.prod(DIMS))
     fields, dt = parity.config_inputs("C4", table, n, "B", ch)
     fields = {k: np.ascontiguousarray(v).copy() for k, v in fields.items()}
@@ -66,7 +69,7 @@ def test_two_rank_slabs_equal_single_process(tmp_path, oracle_lib, synth_table):
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
 
     params, dt, _ = sf.config("C4", synth_table)
-    ch = capi.Chemistry(oracle_lib, is_oracle=True, omp_nthreads=1, **params).initialize()
+    ch = ol.OracleChemistry(oracle_lib, omp_nthreads=1, **params).initialize()
     n = int(np.prod(DIMS))
     fields, dt = parity.config_inputs("C4", synth_table, n, "B", ch)
     g, whole = parity.make_grid(fields, DIMS)
@@ -102,13 +105,14 @@ def _halo_worker(rank, world, port, out_dir):
     import torch
     import torch.distributed as dist
     import parity
+    import oracle_lib as ol
     from grackle_b200 import capi, slabs, synth_fields as sf, synth_tables
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    lib = capi.load_oracle()
+    lib = ol.load_oracle()
     table = synth_tables.ensure()
     params, dt = _halo_params(table)
-    ch = capi.Chemistry(lib, is_oracle=True, omp_nthreads=1, **params).initialize()
+    ch = ol.OracleChemistry(lib, omp_nthreads=1, **params).initialize()
     ni, nj, nk = DIMS_H
     n = ni * nj * nk
     fields, _ = parity.config_inputs("C3", table, n, "B", ch)
@@ -159,7 +163,7 @@ def test_two_rank_halo_exchange_for_h2_self_shielding_1(tmp_path, oracle_lib, sy
     mp.spawn(_halo_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
 
     params, dt = _halo_params(synth_table)
-    ch = capi.Chemistry(oracle_lib, is_oracle=True, omp_nthreads=1, **params).initialize()
+    ch = ol.OracleChemistry(oracle_lib, omp_nthreads=1, **params).initialize()
     ni, nj, nk = DIMS_H
     fields, _ = parity.config_inputs("C3", synth_table, ni * nj * nk, "B", ch)
     g, whole = parity.make_grid(fields, DIMS_H, start=[1, 1, 1], end=[ni - 2, nj - 2, nk - 2],
