@@ -377,8 +377,9 @@ int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, 
                       const double *par_n, const double *par_t, long long n0, long long nt, double zr,
                       double log10_tcmb, cudaStream_t st)
 {
+  // layout: [n_H][T] (cooling, heating) pairs | n_H axis pairs | T axis pairs | cooling at T_CMB per n_H row
   const size_t plane = (size_t)n0 * (size_t)nt;
-  const size_t elems = 2 * plane + (size_t)n0;
+  const size_t elems = 2 * plane + 2 * (size_t)n0 + 2 * (size_t)nt + (size_t)n0;
   if (!c.fast_host) {
     CUDA_OK(cudaMallocHost(&c.fast_host, elems * sizeof(double)));
     CUDA_OK(cudaMalloc(&c.fast, elems * sizeof(double)));
@@ -395,7 +396,19 @@ int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, 
     for (long long i = 0; i < n0; i++) {
       const double *row = cool + (size_t)i * nt;
       const double slope = (row[i2] - row[i2 - 1]) / (par_t[i2] - par_t[i2 - 1]);
-      c.fast_host[2 * plane + i] = (log10_tcmb - par_t[i2 - 1]) * slope + row[i2 - 1];
+      c.fast_host[2 * plane + 2 * n0 + 2 * nt + i] = (log10_tcmb - par_t[i2 - 1]) * slope + row[i2 - 1];
+    }
+    // the stored axis values and the reciprocals of their differences: the interpolation weights
+    // are (x - p_i) / (p_{i+1} - p_i) on the STORED axes (interpolators_g.F:80-98), which are only
+    // nominally uniform - only the index is formed from the mean spacing (:28-29)
+    double *ax0 = c.fast_host + 2 * plane, *ax1 = ax0 + 2 * n0;      // (16-byte aligned: read as double2)
+    for (long long i = 0; i < n0; i++) {
+      ax0[2 * i] = par_n[i];
+      ax0[2 * i + 1] = (i + 1 < n0) ? 1.0 / (par_n[i + 1] - par_n[i]) : 0.0;
+    }
+    for (long long i = 0; i < nt; i++) {
+      ax1[2 * i] = par_t[i];
+      ax1[2 * i + 1] = (i + 1 < nt) ? 1.0 / (par_t[i + 1] - par_t[i]) : 0.0;
     }
     CUDA_OK(cudaMemcpyAsync(c.fast, c.fast_host, elems * sizeof(double), cudaMemcpyHostToDevice, st));
     c.fast_zr = zr;
@@ -403,7 +416,9 @@ int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, 
   }
   d.fast = 1;
   d.ch = c.fast;
-  d.cmb = c.fast + 2 * plane;
+  d.ax[0] = c.fast + 2 * plane;
+  d.ax[1] = d.ax[0] + 2 * n0;
+  d.cmb = d.ax[1] + 2 * nt;
   d.heat_in_ch = heat ? 1 : 0;
   d.par0[0] = par_n[0]; d.par0[1] = par_t[0];
   d.inv_dpar[0] = 1.0 / ((par_n[n0 - 1] - par_n[0]) / (double)(n0 - 1));
@@ -659,11 +674,15 @@ int finish_fields(DeviceCtx *ctx, const GrParams &P, Bound &b)
 int launch_solve(DeviceCtx *ctx, const GrParams &P, const chemistry_data *chem)
 {
   cudaStream_t st = ctx->stream();
-  static int per_sm[4] = {0, 0, 0, 0};
+  static std::atomic<int> per_sm[4];          // resident CTAs per SM by network (0: not asked yet); calls may come from several host threads
   const int pc = chem->primordial_chemistry < 0 ? 0 : (chem->primordial_chemistry > 3 ? 3 : chem->primordial_chemistry);
-  if (per_sm[pc] == 0) per_sm[pc] = grb_solve_max_blocks_per_sm(pc);
+  int occ = per_sm[pc].load(std::memory_order_relaxed);
+  if (occ == 0) {
+    occ = grb_solve_max_blocks_per_sm(pc);
+    per_sm[pc].store(occ, std::memory_order_relaxed);
+  }
   long long want = (P.nactive + GRB_SOLVE_THREADS - 1) / GRB_SOLVE_THREADS;
-  long long cap = (long long)ctx->sm_count * (per_sm[pc] > 0 ? per_sm[pc] : 1);
+  long long cap = (long long)ctx->sm_count * (occ > 0 ? occ : 1);
   const int blocks = (int)(want < cap ? want : cap);
   CUDA_OK(cudaMemsetAsync(ctx->diag, 0, 8 * sizeof(unsigned long long), st));
   CUDA_OK(cudaEventRecord(ctx->ev0, st));
@@ -687,6 +706,11 @@ long long g_pipe_min_cells = 4ll << 20;
 
 bool want_pipeline(const GrParams &P, const grackle_field_data *f)
 {
+  // H2_self_shielding = 1 reads the density of the six neighbours (solve_rate_cool_g.F:1418-1434):
+  // cells of the ghost planes and of chunks that have not arrived yet.  That stencil needs the
+  // whole density array on the device before the first cell runs, so such calls take the plain
+  // copy-in / kernel / copy-out path.
+  if (P.ispecies > 1 && P.iH2shield == 1) return false;
   return g_pipe_shift > 0 && P.nactive >= g_pipe_min_cells && P.nactive <= 0x7fffffffLL &&
          (P.nactive >> g_pipe_shift) >= 2 && !is_device_pointer(f->density);
 }

@@ -65,7 +65,9 @@ struct GrCloudyDev {
   int fdim[2];             // n_H, T points
   const double *ch;        // [n_H][T][2] = (cooling, heating)
   const double *cmb;       // [n_H] cooling at T_CMB
-  double par0[2], inv_dpar[2], fdpar[2];   // axis origin, 1/spacing, spacing
+  const double *ax[2];     // per axis [points][2] = (stored axis value p_i, 1 / (p_{i+1} - p_i)): the stored
+                           // axes are only nominally uniform (CloudyData_noUVB.h5: 10^1.05 written as 11.22018)
+  double par0[2], inv_dpar[2], fdpar[2];   // axis origin, 1/spacing, spacing (index computation only)
 };
 
 // the 15 density-like fields + energy, in the order the kernels index them

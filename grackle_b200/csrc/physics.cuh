@@ -129,9 +129,11 @@ __device__ inline double cloudy_lookup(const GrCloudyDev &c, const double *data,
 // weights not, so it extrapolates linearly like the reference), with
 //   * cooling and heating read as one (cooling, heating) pair per grid point: 4 gathers serve
 //     both lookups instead of 8 gathers + 8 axis gathers,
-//   * axis values formed from origin + i * spacing and divisions by the spacing replaced by
-//     multiplications with its inverse (the grids are uniform; the difference to the stored
-//     axis values is one rounding, ~1e-16),
+//   * the weights (x - p_i) / (p_{i+1} - p_i) from one (p_i, 1 / difference) pair per axis, the
+//     reciprocal formed on the host.  (Round 1 formed p_i as origin + i * spacing: exact on the
+//     synthetic tables, but the real files store rounded axis values - CloudyData_noUVB.h5 has
+//     10^1.05 as 11.22018 - and the real-table parity test of round 2 showed a 4e-6 error in the
+//     cooling rate from it.)
 //   * the CMB-floor term (cooling at T_CMB, cell-invariant along T) read from a per-row array.
 template <class M>
 __device__ __forceinline__ double cloudy_edot_fast_m(M &m, const GrParams &P, const GrCloudyDev &c, double rhoH,
@@ -143,8 +145,10 @@ __device__ __forceinline__ double cloudy_edot_fast_m(M &m, const GrParams &P, co
   i1 = min(c.fdim[0] - 1, max(1, i1));
   int i2 = (int)((log10tem - c.par0[1]) * c.inv_dpar[1]) + 1;
   i2 = min(c.fdim[1] - 1, max(1, i2));
-  const double w1 = (log_n_h - (c.par0[0] + (double)(i1 - 1) * c.fdpar[0])) * c.inv_dpar[0];
-  const double w2 = (log10tem - (c.par0[1] + (double)(i2 - 1) * c.fdpar[1])) * c.inv_dpar[1];
+  const double2 a1 = __ldg(reinterpret_cast<const double2 *>(c.ax[0]) + (i1 - 1));
+  const double2 a2 = __ldg(reinterpret_cast<const double2 *>(c.ax[1]) + (i2 - 1));
+  const double w1 = (log_n_h - a1.x) * a1.y;
+  const double w2 = (log10tem - a2.x) * a2.y;
   const double2 *g = reinterpret_cast<const double2 *>(c.ch) + ((i1 - 1) * c.fdim[1] + (i2 - 1));
   const double2 v00 = __ldg(g), v01 = __ldg(g + 1), v10 = __ldg(g + c.fdim[1]), v11 = __ldg(g + c.fdim[1] + 1);
   const bool floor_on = (icmbTfloor == 1) && ((log10tem - P.log10_tcmb) < 2.0);

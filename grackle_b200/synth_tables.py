@@ -25,7 +25,10 @@ def _axes():
     log_nh = np.linspace(-10.0, 4.0, N_NH)
     # HM2012 tabulates z densely at low z, sparsely above; strictly increasing
     z = np.concatenate([np.linspace(0.0, 5.0, 18), np.linspace(5.6, 15.13, N_Z - 18)])
-    T = 10.0 ** np.linspace(1.0, 9.0, N_T)
+    # the real files store the temperature axis rounded to 7 significant digits (CloudyData_noUVB.h5:
+    # 10, 11.22018, 12.58925, ...), i.e. only nominally uniform in log10 T: reproduce that, because
+    # the interpolation weights must come from the STORED axis values (interpolators_g.F:80-98)
+    T = np.array([float("%.7g" % v) for v in 10.0 ** np.linspace(1.0, 9.0, N_T)])
     return log_nh, z, T
 
 
@@ -122,7 +125,7 @@ def default_path():
     """<repo>/gpurun_out is scratch; keep the generated table next to the package"""
     d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
     os.makedirs(d, exist_ok=True)
-    return os.path.join(d, "CloudyData_UVB=SYNTHETIC_HM2012.h5")
+    return os.path.join(d, "CloudyData_UVB=SYNTHETIC_HM2012_v2.h5")
 
 
 def ensure(path=None):

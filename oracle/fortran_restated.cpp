@@ -1400,8 +1400,8 @@ void make_consistent_g(const FArgs &a)
 long long g_subcycles_sum = 0, g_subcycles_max = 0;
 
 // Conditioning probe (test harness only, OFF by default => bit-exact reference algorithm):
-// multiply edot by (1 + amp*u) and tgas by (1 + 0.01*amp*u'), u in [-1,1] hashed from
-// (cell, iter, seed), in every subcycle.  Running the oracle against itself with
+// multiply edot by (1 + amp*u), tgas by (1 + 0.01*amp*u') and the energy by (1 + 0.01*amp*u''), u in
+// [-1,1] hashed from (cell, iter, seed), in every subcycle.  Running the oracle against itself with
 // amp ~ 1e-13 (edot is a difference of nearly cancelling sums near thermal balance, so a
 // 1-ulp change of one term is a 1e-14..1e-12 relative change of edot) tells which cells'
 // answers are reproducible under round-off-level changes and which are chaotic.
@@ -1465,6 +1465,14 @@ void solve_rate_cool(const FArgs &a, int *ierr)
     for (iter = 1; iter <= a.itmax; iter++) {
       for (int i = is; i <= ie; i++) if (r.itmask[i]) { r.dtit[i] = huge8; sub_sum++; }
 
+      // (probe only) a few-ulp jitter of the cell's energy at the start of the subcycle: every cooling
+      // and heating TERM sees it through the temperature.  A multiplicative factor on the NET edot
+      // alone vanishes with the net at thermal balance - e.g. gas on the CMB floor, where the terms
+      // are orders of magnitude larger than their sum and an implementation's last-bit differences
+      // act on the terms.
+      if (g_noise_amp != 0.0)
+        for (int i = is; i <= ie; i++) if (r.itmask[i])
+          a.e[IDX(a, i, j, k)] *= 1.0 + 0.01 * g_noise_amp * noise_unit(IDX(a, i, j, k), (unsigned long long)iter, g_noise_seed + 155);
       cool1d_multi_g(a, r, j, k, iter, comp1, comp2);
       if (g_noise_amp != 0.0)
         for (int i = is; i <= ie; i++) if (r.itmask[i])

@@ -39,3 +39,9 @@ for pc in range(4):
     np.savez_compressed(os.path.join(OUT, "cooling_rate.pc%d.npz" % pc), **d)
 d = table("cooling_cell.h5")
 np.savez_compressed(os.path.join(OUT, "cooling_cell.npz"), **d)
+
+# the one real new-style Cloudy table of the snapshot (rank 2, 29 x 161; CloudyData_UVB=HM2012.h5 is a
+# missing large blob): copied as DATA so the GPU box, which has no /root/reference, can run
+# tests/test_gpu_parity_large.py::test_real_cloudy_noUVB_table against it
+import shutil
+shutil.copy("/root/reference/grackle_data_files/input/CloudyData_noUVB.h5", os.path.join(OUT, "CloudyData_noUVB.h5"))

@@ -184,3 +184,23 @@ def test_concurrent_calls_from_host_threads(product_lib, synth_table, pipeline):
             assert np.array_equal(ref, tc[i])
     finally:
         cp.free()
+
+
+def test_neighbour_stencil_option_stays_off_the_pipeline(product_lib, synth_table, pipeline):
+    """H2_self_shielding = 1 reads the density of the six neighbours, ghost planes included; the
+    chunked pipeline only stages the active range chunk by chunk, so such calls must take the plain
+    path whatever the pipeline settings say (round-1 advisor finding): a small chunk size with a ghost
+    layer gives bit for bit the result of the pipeline switched off."""
+    dims = [18, 12, 10]
+    start, end = [1, 1, 1], [16, 10, 8]
+    cp, fields, dt = _inputs("C3", synth_table, product_lib, int(np.prod(dims)), over=dict(H2_self_shielding=1))
+    dx = 3.0e17 / sf.config("C3", synth_table)[0]["length_units"]
+    try:
+        pipeline(0, 1)
+        ref, st0 = _solve(cp, fields, dims, dt, start=start, end=end, dx=dx)
+        pipeline(4, 1)                        # 16-cell chunks: would read unstaged neighbours if it ran
+        out, st1 = _solve(cp, fields, dims, dt, start=start, end=end, dx=dx)
+        _same(ref, out)
+        assert st0.subcycles_sum == st1.subcycles_sum
+    finally:
+        cp.free()
