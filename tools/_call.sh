@@ -1,3 +1,4 @@
 cd $GRAFT_REPO_ROOT
-mkdir -p gpurun_out
-tools/bench_variants.sh "main vt640 vt384" 24 C4 > gpurun_out/r2c6_variants.log 2>&1; cat gpurun_out/r2c6_variants.log
+mkdir -p gpurun_out; rm -f gpurun_out/parity_large.txt
+( time python -m pytest tests -m gpu -q --durations=6 ) > gpurun_out/r2d1_tests.log 2>&1; tail -45 gpurun_out/r2d1_tests.log | cut -c1-700
+grep -v calculate_ gpurun_out/parity_large.txt
