@@ -184,6 +184,27 @@ void grb200_set_solve_variant(int variant);
  * pipeline off (copy everything in, run, copy everything back).  Results are identical. */
 void grb200_set_host_pipeline(int log2_chunk_cells, long long min_cells);
 
+/* calculate_dust_temperature for callers that must not trigger a device or host allocation (code
+   under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO
+   counterpart in the reference.
+   Same arguments and result as local_calculate_dust_temperature, with these limits:
+     * every field array it reads (density, HI, HII, [H2I, H2II, HM], e, HeI, HeII, HeIII,
+       internal_energy, [metal_density], [isrf_habing]) and `dust_temperature` must be DEVICE (or managed)
+       memory of the chemistry object's GPU; host arrays are rejected (staging them would allocate);
+     * primordial_chemistry >= 1 (the tabulated pc = 0 temperature needs per-call Cloudy planes);
+     * the grid holds at most GRB200_NOALLOC_MAX_CELLS cells (all cells, ghost zones included):
+       the gas temperature between its two kernels lives in a static device array of that size
+       (8 MiB, held by every GPU that loads the library until exit).  Larger grids return FAIL
+       with a message; so does anything else above.
+   It calls no cudaMalloc / cudaFree / cudaMallocHost or other allocating routine.  All calls share
+   the one scratch array (nothing in it has to start at zero: every active cell is written before it
+   is read), so calls that overlap on the GPU - other streams, other chemistry objects on the same
+   device - race; serialise them. */
+#define GRB200_NOALLOC_MAX_CELLS (1 << 20)
+int grb200_calculate_dust_temperature_noalloc(chemistry_data *my_chemistry, chemistry_data_storage *my_rates,
+                                              code_units *my_units, grackle_field_data *my_fields,
+                                              gr_float *dust_temperature);
+
 #ifdef __cplusplus
 }
 #endif

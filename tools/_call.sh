@@ -1,4 +1,4 @@
 cd $GRAFT_REPO_ROOT
-mkdir -p gpurun_out; rm -f gpurun_out/parity_large.txt
-( time python -m pytest tests -m gpu -q --durations=6 ) > gpurun_out/r2d1_tests.log 2>&1; tail -45 gpurun_out/r2d1_tests.log | cut -c1-700
-grep -v calculate_ gpurun_out/parity_large.txt
+mkdir -p gpurun_out
+python -m pytest tests/test_zz_no_alloc.py -m gpu -q 2>&1 | tail -5
+python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_parity_large.py 2>&1 | tail -5
