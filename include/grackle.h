@@ -200,7 +200,7 @@ void grb200_set_host_pipeline(int log2_chunk_cells, long long min_cells);
    the one scratch array (nothing in it has to start at zero: every active cell is written before it
    is read), so calls that overlap on the GPU - other streams, other chemistry objects on the same
    device - race; serialise them. */
-#define GRB200_NOALLOC_MAX_CELLS (1 << 20)
+#define GRB200_NOALLOC_MAX_CELLS 1048576   /* 2^20 */
 int grb200_calculate_dust_temperature_noalloc(chemistry_data *my_chemistry, chemistry_data_storage *my_rates,
                                               code_units *my_units, grackle_field_data *my_fields,
                                               gr_float *dust_temperature);
