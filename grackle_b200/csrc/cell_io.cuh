@@ -134,6 +134,17 @@ __device__ __forceinline__ void store_cell(const GrParams &P, size_t x, Cell &c)
 // prefetch.global.L1 of the stage-4 chemistry row issued before stage 2 (-4 %), and passing
 // (weight, offset) through a shared-memory mailbox instead of the three shuffles were all
 // measured slower than this loop as the compiler schedules it.)
+// Row offsets are non-negative and < 2^32: added as UNSIGNED 32-bit values so that the load can
+// take the "64-bit base + 32-bit offset" address form instead of a sign extension and a 64-bit
+// add per address (GRB_OFF_SIGNED=1 restores the signed form for comparison).
+#ifndef GRB_OFF_SIGNED
+#define GRB_OFF_SIGNED 0
+#endif
+#if GRB_OFF_SIGNED
+#define GRB_OFF(x) (x)
+#else
+#define GRB_OFF(x) ((unsigned)(x))
+#endif
 template <int G, int NCOLS, int ROWB, int CS>
 __device__ __forceinline__ void coop_fetch(const double *table, int my_off, double my_t, double *dst0)
 {
@@ -153,7 +164,7 @@ __device__ __forceinline__ void coop_fetch(const double *table, int my_off, doub
 #pragma unroll
     for (int k = 0; k < PER; k++) {
       if ((k + 1) * G <= NCOLS || g + k * G < NCOLS) {
-        const double2 p = __ldg(reinterpret_cast<const double2 *>(src + off + 16 * k * G));
+        const double2 p = __ldg(reinterpret_cast<const double2 *>(src + GRB_OFF(off) + 16 * k * G));
         dst[pass * CPP + k * G * CS] = p.x + p.y * t;
       }
     }
@@ -197,11 +208,11 @@ __device__ __forceinline__ void coop_fetch2(const double *table1, int my_off1, d
 #pragma unroll
       for (int k = 0; k < PER1; k++)
         if ((k + 1) * G <= NC1 || g + k * G < NC1)
-          p1[b][k] = __ldg(reinterpret_cast<const double2 *>(src1 + off1 + 16 * k * G));
+          p1[b][k] = __ldg(reinterpret_cast<const double2 *>(src1 + GRB_OFF(off1) + 16 * k * G));
 #pragma unroll
       for (int k = 0; k < PER2; k++)
         if ((k + 1) * G <= NC2 || g + k * G < NC2)
-          p2[b][k] = __ldg(reinterpret_cast<const double2 *>(src2 + off2 + 16 * k * G));
+          p2[b][k] = __ldg(reinterpret_cast<const double2 *>(src2 + GRB_OFF(off2) + 16 * k * G));
     }
 #pragma unroll
     for (int b = 0; b < NB; b++) {

@@ -134,15 +134,26 @@ __global__ void __launch_bounds__(128) k_dust_temperature(const __grid_constant_
 // log-T bin, warp-cooperative coalesced fetch of the cooling-table row into shared-memory
 // slots (per-thread gathers kept the L1 at ~3/4 of its wavefront rate), log/exp table in
 // shared memory.  VAR: optional physics modules folded away at compile time, as for k_solve.
+// Block shape (pc = 3 compact variant, 67 M cells, Gcell/s): round 1 shipped 64-thread blocks, 14 per
+// SM by shared memory (17.2).  Round 2: the compact variant keeps only the 20 cooling columns it
+// reads (13.8 -> 11.7 KB of slots per 64 threads) and its occupancy is pinned through
+// __launch_bounds__: 64 threads x 12 / 14 / 16 blocks (80 / 71 / 64 registers) 16.6 / 17.9 / 16.1,
+// 128 threads x 7 / 8 blocks (71 / 64 registers) 17.8 / 19.05.  The other variants need more
+// registers and keep the compiler's choice.
 #ifndef GRB_CT_THREADS
-#define GRB_CT_THREADS 64    /* 2-warp blocks, 14 per SM: +4.4 % over 128 (17.2 vs 16.5 Gcell/s, pc=3 compact) */
+#define GRB_CT_THREADS 128
 #endif
+#ifndef GRB_CT_MINBLOCKS
+#define GRB_CT_MINBLOCKS (1024 / GRB_CT_THREADS)   /* compact variant: 32 warps per SM at 64 registers */
+#endif
+__host__ __device__ constexpr int ct_minblocks(int var) { return var == VAR_LEAN ? GRB_CT_MINBLOCKS : (640 / GRB_CT_THREADS > 0 ? 640 / GRB_CT_THREADS : 1); }
 template <int PC, int VAR>
-__global__ void __launch_bounds__(GRB_CT_THREADS) k_cooling_time(const __grid_constant__ GrParams P0)
+__global__ void __launch_bounds__(GRB_CT_THREADS, ct_minblocks(VAR)) k_cooling_time(const __grid_constant__ GrParams P0)
 {
   constexpr int G = coop_lanes(PC);
   constexpr int CS = slot_col_stride(GRB_CT_THREADS, G);      // column-major slots (network.cuh)
-  __shared__ double ct_slots[NCOOL * CS];
+  constexpr int NCA = cool_cols(PC, VAR == VAR_LEAN);         // the compact variant reads no dust / CIE columns
+  __shared__ double ct_slots[NCA * CS];
   __shared__ double ct_fm[GRB_FM_TABLE_DOUBLES];
   // the block's copy of the log/exp table: loads issued here, stored to shared memory only
   // after the cell's field loads are in flight too (one memory round trip instead of two).
@@ -188,7 +199,7 @@ __global__ void __launch_bounds__(GRB_CT_THREADS) k_cooling_time(const __grid_co
       tdef = ti.tdef;
     }
   }
-  if (PC > 1 || anydust) coop_fetch<G, NCOOL, NCOOL * 16, CS>(P.cool, off, tdef, warp_slots);
+  if (PC > 1 || anydust) coop_fetch<G, NCA, NCOOL * 16, CS>(P.cool, off, tdef, warp_slots);
   else if (PC == 1) coop_fetch<G, L_BREM + 1, NCOOL * 16, CS>(P.cool, off, tdef, warp_slots);
   __syncwarp();
   if (valid) {

@@ -1,4 +1,6 @@
 cd $GRAFT_REPO_ROOT
-mkdir -p gpurun_out
-python -m pytest tests/test_zz_no_alloc.py -m gpu -q 2>&1 | tail -5
-python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_parity_large.py 2>&1 | tail -5
+for v in v0 vc64m12 vc64m14 vc64m16 vc128m7 vc128m8; do
+  so=$PWD/grackle_b200/lib_$v/libgrackle_b200.so; [ -f $so ] || continue
+  echo "== $v"; GRB200_LIB=$so python tools/calc_probe.py 64 cooling_time 2>&1 | grep Gcell
+done
+echo "== solve u/s"; tools/bench_variants.sh "vu vs" 24 C4 2>&1 | grep -E "==|Mcell"
