@@ -24,6 +24,35 @@ def slab_view(arrays, dims, world, rank):
     return {k: v[lo:hi] for k, v in arrays.items()}, [ni, nj, k1 - k0], lo
 
 
+def interleaved_planes(nk_global, world, rank):
+    """k-planes of rank under the k-mod-N interleave (the remedy when contiguous slabs
+    differ in cost): planes rank, rank + world, rank + 2 world, ...  Each plane is still one contiguous
+    address range per field, so a rank's share is nk_global / world separate one-plane grids - or, for
+    fields the rank generates or receives itself, one local array whose plane j is global plane
+    j * world + rank."""
+    return list(range(int(rank), int(nk_global), int(world)))
+
+
+def local_to_global_cells(local_ids, plane_cells, world, rank, interleave, cells_per_rank):
+    """global cell ids of a rank's local cells: contiguous slab (offset) or k-mod-N interleave"""
+    if not interleave:
+        return local_ids + rank * cells_per_rank
+    j = local_ids // plane_cells
+    return (j * world + rank) * plane_cells + (local_ids - j * plane_cells)
+
+
+def imbalance(times, dist=None, device=None):
+    """max / mean over ranks of a per-rank time (1.0 = perfectly balanced); also returns the list"""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return 1.0, [float(times)]
+    import torch
+    mine = torch.tensor([float(times)], dtype=torch.float64, device=device)
+    allt = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(allt, mine)
+    v = [float(t.item()) for t in allt]
+    return max(v) / (sum(v) / len(v)), v
+
+
 def allreduce_diagnostics(stats, dist=None, device=None):
     """stats: dict with subcycles_sum, subcycles_max, cells_hit_itmax, cells_nan, cells.
     SUM for counts, MAX for the longest cell.  dist=None (single process) returns stats."""

@@ -86,6 +86,11 @@ CONFIGS = {
     "C3": (dict(primordial_chemistry=2, metal_cooling=1, UVbackground=1, h2_on_dust=1,
                 self_shielding_method=3), proper_units(), 3.15e13, (256, 256, 256)),
     "C4": (dict(primordial_chemistry=3, metal_cooling=1, UVbackground=1), cosmology_units(), 3.15e13, (1024, 1024, 1024)),
+    # the parameter set of the reference's own examples and timing harness (c_example.c:52-70,
+    # cxx_omp_example.C:160-193): pc = 3 + dust_chemistry (which switches on H2 on dust, grain
+    # recombination cooling and photo-electric heating 2) + metals + UVB, proper units, input Set H
+    "HARNESS": (dict(primordial_chemistry=3, dust_chemistry=1, metal_cooling=1, UVbackground=1), proper_units(),
+                3.15e13, (128, 128, 128)),
 }
 
 
@@ -108,8 +113,9 @@ def fields_for(pc):
 
 
 def make_fields(index, pc, units, temperature_units, set_name="B", fh=0.76, gamma=5.0 / 3.0,
-                dtoh=6.8e-5):
-    """index: int64 global cell ids.  Returns dict field-name -> float64 array (code units)."""
+                dtoh=6.8e-5, set_c_geometry=(1024 * 1024, 1024)):
+    """index: int64 global cell ids.  Returns dict field-name -> float64 array (code units).
+    set_c_geometry = (cells per k-plane, k-planes of the GLOBAL grid), used by Set C only."""
     xp_log10 = (lambda t: t.log10()) if _is_torch(index) else np.log10
     out = {}
     if set_name == "H":
@@ -137,7 +143,17 @@ def make_fields(index, pc, units, temperature_units, set_name="B", fh=0.76, gamm
         return {k: out[k] for k in fields_for(pc)}
 
     u = lambda s: uniform(index, SEED_B, s)
-    n_h = _pow10(-4.0 + 6.0 * u(0))                 # proper cm^-3
+    if set_name == "C":
+        # Set C = Set B with SPATIAL STRUCTURE along k (the slab axis of the multi-GPU decomposition):
+        # the density rises by five decades from the first to the last k-plane of the global grid, with
+        # one decade of cell-to-cell scatter, so subcycle counts - hence k-slab run times - differ
+        # several-fold between slabs (Set B is i.i.d.: every slab costs the same by construction)
+        plane, nk = set_c_geometry
+        s_k = (index // plane) % nk
+        s_k = (s_k.to(u(0).dtype) if _is_torch(index) else s_k.astype(np.float64)) / float(nk)
+        n_h = _pow10(-4.0 + 5.0 * s_k + 1.0 * u(0))
+    else:
+        n_h = _pow10(-4.0 + 6.0 * u(0))             # proper cm^-3
     T = _pow10(2.0 + 5.0 * u(1))                    # K
     zmet = _pow10(-3.0 + 3.0 * u(2))                # Z / Zsun
     xe = _pow10(-4.0 + 4.0 * u(3))                  # ionised fraction of H

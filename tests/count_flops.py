@@ -37,11 +37,12 @@ def main():
     table = synth_tables.ensure()
     out = {"cells": n, "input_set": "B", "note": "one flop per add/sub/mul/div/compare and per elementary-function call; "
            "max/min count as one compare; sign flips and abs are free; table/field loads are not counted"}
-    for name in ("C1", "C2", "C3", "C4"):
+    for name in ("C1", "C2", "C3", "C4", "HARNESS"):
+        set_name = "H" if name == "HARNESS" else "B"       # the harness configuration is quoted on its own input set
         params, dt, _ = sf.config(name, table)
         cc = ol.OracleChemistry(cnt, omp_nthreads=1, **params).initialize()
         cr = ol.OracleChemistry(ref, omp_nthreads=1, **params).initialize()
-        fields, dt = parity.config_inputs(name, table, n, "B", cr)
+        fields, dt = parity.config_inputs(name, table, n, set_name, cr)
         dims = [1, n]      # one cell per row: the reference works row-at-a-time with masks, and finished
                            # cells of a longer row would still be charged the row-level comparisons
         # the counting build must give the plain build's answer bit for bit
@@ -57,7 +58,7 @@ def main():
         arith = c["add_sub"] + c["mul"] + c["div"] + c["compare"]
         fn = c["log"] + c["exp"] + c["pow"] + c["sqrt"] + c["other"]
         per = {k: v / subs for k, v in c.items()}
-        rec = {"subcycles_per_cell": subs / n, "per_cell_subcycle": per,
+        rec = {"input_set": set_name, "subcycles_per_cell": subs / n, "per_cell_subcycle": per,
                "flops_per_cell_subcycle": (arith + fn) / subs}
         # one cooling-time evaluation (config C5 uses C4's parameters)
         tc = np.zeros(n)

@@ -1,6 +1,13 @@
 cd $GRAFT_REPO_ROOT
-for v in v0 vc64m12 vc64m14 vc64m16 vc128m7 vc128m8; do
-  so=$PWD/grackle_b200/lib_$v/libgrackle_b200.so; [ -f $so ] || continue
-  echo "== $v"; GRB200_LIB=$so python tools/calc_probe.py 64 cooling_time 2>&1 | grep Gcell
-done
-echo "== solve u/s"; tools/bench_variants.sh "vu vs" 24 C4 2>&1 | grep -E "==|Mcell"
+mkdir -p gpurun_out
+( time python bench.py --nk 8 --steps 1 --warmup 1 > gpurun_out/r2d3_bench_small.json 2> gpurun_out/r2d3_bench_small.err ); tail -5 gpurun_out/r2d3_bench_small.err | cut -c1-300
+python - <<'PY'
+import json
+d=json.load(open("gpurun_out/r2d3_bench_small.json"))
+print("value %.3g e2e %.3g pageable %s" % (d["value"], d["e2e"]["value"], d["e2e_pageable"] and "%.3g" % d["e2e_pageable"]["value"]))
+print("roofline", {k: d["roofline"][k] for k in ("achieved","peak","frac","peak_theoretical","frac_of_theoretical")})
+print("sweep", {k: round(v["frac_hbm"],3) for k,v in d["calculate_sweep"].items()})
+for k,v in d["configs"].items(): print(k, "%.3g cells/s" % v["cells_per_s"], "sub/cell %.1f" % v["subcycles_per_cell"], "frac %.3f" % v["roofline_frac_fp64"], "err", v.get("max_rel_err"), "itmax", v["cells_hit_itmax"])
+print("set_c", d["set_c"]["contiguous_k_slabs"]["cells_per_s"], d["set_c"]["contiguous_k_slabs"]["subcycles_per_cell"])
+print("cpu", d["cpu_baseline"]["value"], d["cpu_baseline"]["cores"])
+PY
