@@ -266,3 +266,48 @@ def test_compact_solve_kernels_keep_their_state_in_registers():
     for name, (reg, stack) in usage.items():
         if "k_solve" in name:
             assert reg <= 128 and stack <= 512, (name, reg, stack)
+
+
+def _member_probe(include_dirs, tmp_path, tag, extra=()):
+    """offsetof() of EVERY member of the four ABI structs, as the C compiler sees the given headers"""
+    structs = [("chemistry_data", [n for n, _ in capi._CHEM_FIELDS if n != "omp_nthreads"]),
+               ("code_units", [n for n, _ in capi.CodeUnits._fields_]),
+               ("grackle_field_data", [n for n, _ in capi.FieldData._fields_]),
+               ("chemistry_data_storage", [n for n, _ in capi.ChemistryStorage._fields_])]
+    lines = ["#include <stdio.h>", "#include <stddef.h>", '#include "grackle.h"', "int main(void) {"]
+    for sname, members in structs:
+        lines.append('  printf("%s.sizeof %%zu\\n", sizeof(%s));' % (sname, sname))
+        for m in members:
+            lines.append('  printf("%s.%s %%zu\\n", offsetof(%s, %s));' % (sname, m, sname, m))
+    lines += ["  return 0;", "}"]
+    src = tmp_path / ("members_%s.c" % tag)
+    src.write_text("\n".join(lines))
+    exe = tmp_path / ("members_%s" % tag)
+    subprocess.run(["gcc", "-std=gnu99"] + list(extra) + ["-I%s" % d for d in include_dirs] + [str(src), "-o", str(exe)],
+                   check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout
+    return dict(ln.split() for ln in out.strip().splitlines())
+
+
+def test_every_struct_member_offset(tmp_path):
+    """every member of chemistry_data, code_units, grackle_field_data and chemistry_data_storage sits where
+    (a) the ctypes mirror the tests use and (b) the reference's own headers put it (the
+    earlier probe checked five offsets)"""
+    ours = _member_probe([INCLUDE], tmp_path, "ours")
+    mirrors = {"chemistry_data": capi.ChemistryData, "code_units": capi.CodeUnits, "grackle_field_data": capi.FieldData,
+               "chemistry_data_storage": capi.ChemistryStorage}
+    checked = 0
+    for key, off in ours.items():
+        sname, member = key.split(".")
+        if member == "sizeof":
+            continue
+        assert getattr(mirrors[sname], member).offset == int(off), key
+        checked += 1
+    assert checked >= 185, checked          # 189 members (nested table structs are covered by the offsets that follow them)
+    ref = "/root/reference/src/clib"
+    if os.path.isdir(ref):
+        for extra in ([], ["-fopenmp"]):          # callers built with and without OpenMP
+            a = _member_probe([INCLUDE], tmp_path, "ours%d" % len(extra), extra=extra)
+            b = _member_probe([os.path.join(ROOT, "oracle", "_ref"), ref], tmp_path, "ref%d" % len(extra),
+                              extra=["-DLINUX"] + extra)
+            assert a == b, {k: (a[k], b.get(k)) for k in a if a[k] != b.get(k)}
