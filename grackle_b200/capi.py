@@ -175,6 +175,10 @@ def load_product():
     lib.grb200_set_solve_variant.restype = None
     lib.grb200_set_host_pipeline.argtypes = [C.c_int, C.c_longlong]
     lib.grb200_set_host_pipeline.restype = None
+    lib.grb200_set_devices.argtypes = [C.POINTER(ChemistryData), C.POINTER(ChemistryStorage), C.c_int, C.c_int]
+    lib.grb200_set_devices.restype = C.c_int
+    lib.grb200_get_devices.argtypes = [C.POINTER(ChemistryStorage)]
+    lib.grb200_get_devices.restype = C.c_int
     return lib
 
 

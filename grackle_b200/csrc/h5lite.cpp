@@ -13,6 +13,21 @@ template <typename T> T File::rd(uint64_t off) const
   return v;
 }
 
+// one byte, 0 beyond the end of the file (a truncated or corrupt file must fail, not fault)
+unsigned File::byte(uint64_t off) const { return in_range(off, 1) ? buf_[off] : 0u; }
+
+// NUL-terminated name starting at off, bounded by the end of the file (and by max_len when given)
+bool File::cstring(uint64_t off, uint64_t max_len, std::string *out) const
+{
+  if (!in_range(off, 1)) return false;
+  uint64_t room = buf_.size() - off;
+  if (max_len && max_len < room) room = max_len;
+  const void *nul = std::memchr(buf_.data() + off, 0, room);
+  if (!nul && !max_len) return false;                      // runs off the end of the file
+  out->assign((const char *)buf_.data() + off, nul ? (size_t)((const unsigned char *)nul - (buf_.data() + off)) : (size_t)room);
+  return true;
+}
+
 const Node *Node::find(const std::string &path) const
 {
   const Node *n = this;
@@ -137,17 +152,18 @@ bool File::read_object(uint64_t addr, Node *node, int depth)
           const uint64_t btree = base_ + rd<uint64_t>(body), heap = base_ + rd<uint64_t>(body + 8);
           if (!in_range(heap, 32) || std::memcmp(buf_.data() + heap, "HEAP", 4) != 0)
             return fail("bad local heap");
-          if (!read_btree(btree, base_ + rd<uint64_t>(heap + 24), node, depth)) return false;
+          if (!read_btree(btree, base_ + rd<uint64_t>(heap + 24), node, depth, 0)) return false;
           break;
         }
         case 0x0C: {
+          if (!in_range(body, 8)) return fail("attribute message out of range");
           if (buf_[body] != 1) break;
           auto pad8 = [](uint64_t x) { return (x + 7) & ~7ull; };
           const unsigned nsz = rd<uint16_t>(body + 2), dtsz = rd<uint16_t>(body + 4),
                          dssz = rd<uint16_t>(body + 6);
           uint64_t q = body + 8;
-          if (!in_range(q, nsz)) return fail("attribute name out of range");
-          std::string name((const char *)buf_.data() + q);
+          std::string name;
+          if (nsz == 0 || !in_range(q, nsz) || !cstring(q, nsz, &name)) return fail("attribute name out of range");
           q += pad8(nsz);
           Dtype adt;
           std::vector<uint64_t> adims;
@@ -170,6 +186,7 @@ bool File::read_object(uint64_t addr, Node *node, int depth)
     node->is_dataset = true;
     node->data.dims = dims;
     const size_t n = node->data.count();
+    if (!in_range(layout, 18)) return fail("layout message out of range");
     const unsigned ver = buf_[layout];
     uint64_t data_off = ~0ull;
     if (ver == 3) {
@@ -190,24 +207,27 @@ bool File::read_object(uint64_t addr, Node *node, int depth)
   return true;
 }
 
-bool File::read_btree(uint64_t na, uint64_t heap_data, Node *node, int depth)
+bool File::read_btree(uint64_t na, uint64_t heap_data, Node *node, int depth, int tree_depth)
 {
+  if (tree_depth > 8) return fail("B-tree too deep (corrupt file?)");
   if (!in_range(na, 24) || std::memcmp(buf_.data() + na, "TREE", 4) != 0) return fail("bad B-tree node");
   const unsigned level = buf_[na + 5], nent = rd<uint16_t>(na + 6);
+  if (!in_range(na + 24, 8 + 16ull * nent)) return fail("B-tree node runs past end of file");
   for (unsigned i = 0; i < nent; ++i) {
     const uint64_t child = base_ + rd<uint64_t>(na + 24 + 8 + 16ull * i);
     if (level > 0) {
-      if (!read_btree(child, heap_data, node, depth)) return false;
+      if (!read_btree(child, heap_data, node, depth, tree_depth + 1)) return false;
       continue;
     }
     if (!in_range(child, 8) || std::memcmp(buf_.data() + child, "SNOD", 4) != 0)
       return fail("bad symbol-table node");
     const unsigned nsym = rd<uint16_t>(child + 6);
+    if (!in_range(child + 8, 40ull * nsym)) return fail("symbol-table node runs past end of file");
     for (unsigned s = 0; s < nsym; ++s) {
       const uint64_t e = child + 8 + 40ull * s;
       const uint64_t name_off = heap_data + rd<uint64_t>(e);
-      if (!in_range(name_off, 1)) return fail("symbol name out of range");
-      std::string name((const char *)buf_.data() + name_off);
+      std::string name;
+      if (!cstring(name_off, 0, &name)) return fail("symbol name out of range");
       if (!read_object(base_ + rd<uint64_t>(e + 8), &node->children[name], depth + 1)) return false;
     }
   }

@@ -52,7 +52,9 @@ class File {
   bool parse_space(uint64_t off, std::vector<uint64_t> *dims);
   void decode(const Dtype &dt, const std::vector<uint64_t> &dims, uint64_t off, Value *out);
   bool read_object(uint64_t addr, Node *node, int depth);
-  bool read_btree(uint64_t node_addr, uint64_t heap_data, Node *node, int depth);
+  bool read_btree(uint64_t node_addr, uint64_t heap_data, Node *node, int depth, int tree_depth);
+  unsigned byte(uint64_t off) const;
+  bool cstring(uint64_t off, uint64_t max_len, std::string *out) const;
   bool fail(const std::string &m) { if (err_.empty()) err_ = m; return false; }
 };
 

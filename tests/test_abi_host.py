@@ -311,3 +311,61 @@ def test_every_struct_member_offset(tmp_path):
             b = _member_probe([os.path.join(ROOT, "oracle", "_ref"), ref], tmp_path, "ref%d" % len(extra),
                               extra=["-DLINUX"] + extra)
             assert a == b, {k: (a[k], b.get(k)) for k in a if a[k] != b.get(k)}
+
+
+def test_damaged_table_files_fail_cleanly(synth_table, tmp_path):
+    """round-1 advisor finding: the hand-written HDF5 reader (h5lite.cpp) must turn a truncated or
+    corrupt grackle_data_file into FAIL - never into an out-of-bounds read or endless recursion.
+    The child process loads ~100 deterministically damaged copies of the synthetic table
+    (truncations, overwritten metadata windows, self-referencing B-tree children); it must survive
+    all of them, refuse every truncated file, and still load the intact one."""
+    code = r"""
+import sys, os, numpy as np
+sys.path.insert(0, %r)
+from grackle_b200 import capi, synth_fields as sf
+lib = capi.load_product()
+good = %r
+raw = open(good, "rb").read()
+tmp = %r
+rng = np.random.default_rng(7)
+def attempt(data, tag):
+    path = os.path.join(tmp, "damaged.h5")
+    open(path, "wb").write(data)
+    params, dt, _ = sf.config("C4", path)
+    try:
+        capi.Chemistry(lib, **params).initialize().free()
+        return True
+    except RuntimeError:
+        return False
+assert attempt(raw, "intact")
+n_fail = 0
+for frac in (0.0, 0.001, 0.01, 0.05, 0.1, 0.3, 0.5, 0.7, 0.9, 0.99, 0.999):
+    ok = attempt(raw[:int(len(raw) * frac)], "trunc")
+    assert not ok, "truncated file (%%g) was accepted" %% frac
+    n_fail += 1
+# metadata lives in object headers / B-trees / heaps scattered through the file: overwrite windows
+for trial in range(90):
+    b = bytearray(raw)
+    pos = int(rng.integers(8, len(b) - 64))
+    if trial %% 3 == 0:
+        pos = int(rng.integers(8, 4096))
+    w = int(rng.integers(1, 48))
+    fill = (0xFF, 0x00, None)[trial %% 3]
+    b[pos:pos + w] = bytes([fill]) * w if fill is not None else rng.integers(0, 256, w, dtype=np.uint8).tobytes()
+    n_fail += 0 if attempt(bytes(b), "window") else 1
+# every B-tree node pointing at itself (cycle)
+b = bytearray(raw)
+at = 0
+while True:
+    at = raw.find(b"TREE", at)
+    if at < 0: break
+    level = 1
+    b[at + 5] = level
+    b[at + 24 + 8: at + 24 + 16] = int(at).to_bytes(8, "little")
+    at += 4
+assert not attempt(bytes(b), "cycle")
+print("survived, refused", n_fail + 1)
+""" % (ROOT, synth_table, str(tmp_path))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout[-2000:], r.stderr[-2000:])
+    assert "survived" in r.stdout
