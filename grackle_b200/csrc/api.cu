@@ -439,31 +439,36 @@ int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, 
                       const double *par_n, const double *par_t, long long n0, long long nt, double zr,
                       double log10_tcmb, cudaStream_t st)
 {
-  // layout: [n_H][T] (cooling, heating) pairs | n_H axis pairs | T axis pairs | cooling at T_CMB per n_H row
+  // layout: [n_H][T] entries of 4 doubles: (cooling, heating) of the point and of its right-hand T neighbour
+  // (one 256-bit load per row of corners) | n_H axis pairs | T axis pairs | cooling at T_CMB per n_H row
   const size_t plane = (size_t)n0 * (size_t)nt;
-  const size_t elems = 2 * plane + 2 * (size_t)n0 + 2 * (size_t)nt + (size_t)n0;
+  constexpr size_t EN = GRB_CLOUDY_ENTRY;
+  const size_t elems = EN * plane + 2 * (size_t)n0 + 2 * (size_t)nt + (size_t)n0;
   if (!c.fast_host) {
     CUDA_OK(cudaMallocHost(&c.fast_host, elems * sizeof(double)));
     CUDA_OK(cudaMalloc(&c.fast, elems * sizeof(double)));
   }
   if (!c.fast_valid || c.fast_zr != zr) {
     CUDA_OK(cudaStreamSynchronize(st));
-    for (size_t q = 0; q < plane; q++) {
-      c.fast_host[2 * q] = cool[q];
-      c.fast_host[2 * q + 1] = heat ? heat[q] : 0.0;
-    }
+    for (long long i = 0; i < n0; i++)
+      for (long long t = 0; t < nt; t++) {
+        const size_t q = (size_t)i * nt + t, qr = (t + 1 < nt) ? q + 1 : q;
+        double *e = c.fast_host + EN * q;
+        e[0] = cool[q]; e[1] = heat ? heat[q] : 0.0;
+        if (EN == 4) { e[2] = cool[qr]; e[3] = heat ? heat[qr] : 0.0; }
+      }
     const double dpar_t = (par_t[nt - 1] - par_t[0]) / (double)(nt - 1);
     long long i2 = (long long)((log10_tcmb - par_t[0]) / dpar_t) + 1;
     i2 = std::min(nt - 1, std::max(1LL, i2));
     for (long long i = 0; i < n0; i++) {
       const double *row = cool + (size_t)i * nt;
       const double slope = (row[i2] - row[i2 - 1]) / (par_t[i2] - par_t[i2 - 1]);
-      c.fast_host[2 * plane + 2 * n0 + 2 * nt + i] = (log10_tcmb - par_t[i2 - 1]) * slope + row[i2 - 1];
+      c.fast_host[EN * plane + 2 * n0 + 2 * nt + i] = (log10_tcmb - par_t[i2 - 1]) * slope + row[i2 - 1];
     }
     // the stored axis values and the reciprocals of their differences: the interpolation weights
     // are (x - p_i) / (p_{i+1} - p_i) on the STORED axes (interpolators_g.F:80-98), which are only
     // nominally uniform - only the index is formed from the mean spacing (:28-29)
-    double *ax0 = c.fast_host + 2 * plane, *ax1 = ax0 + 2 * n0;      // (16-byte aligned: read as double2)
+    double *ax0 = c.fast_host + EN * plane, *ax1 = ax0 + 2 * n0;      // (16-byte aligned: read as double2)
     for (long long i = 0; i < n0; i++) {
       ax0[2 * i] = par_n[i];
       ax0[2 * i + 1] = (i + 1 < n0) ? 1.0 / (par_n[i + 1] - par_n[i]) : 0.0;
@@ -478,7 +483,7 @@ int cloudy_fast_plane(GrCloudyDev &d, DeviceCtx::Cloudy &c, const double *cool, 
   }
   d.fast = 1;
   d.ch = c.fast;
-  d.ax[0] = c.fast + 2 * plane;
+  d.ax[0] = c.fast + EN * plane;
   d.ax[1] = d.ax[0] + 2 * n0;
   d.cmb = d.ax[1] + 2 * nt;
   d.heat_in_ch = heat ? 1 : 0;
@@ -742,11 +747,15 @@ int finish_fields(DeviceCtx *ctx, const GrParams &P, Bound &b)
 {
   cudaStream_t st = ctx->stream();
   if (!b.on_device) {
+    // only the k-planes that hold active cells go back: nothing else was written, and the planes
+    // outside may belong to another slab of a dispatched call (the halo of H2_self_shielding = 1),
+    // whose owner is writing them at this moment
+    const size_t plane = (size_t)P.in * P.jn, first = plane * (size_t)P.ks, count = plane * (size_t)(P.ke - P.ks + 1);
     for (const FieldSpec &s : b.fields)
       if (s.writeback)
-        CUDA_OK(cudaMemcpyAsync(s.ptr, P.f[s.id], b.n * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaMemcpyAsync(s.ptr + first, P.f[s.id] + first, count * sizeof(double), cudaMemcpyDeviceToHost, st));
     if (b.out_user)
-      CUDA_OK(cudaMemcpyAsync(b.out_user, b.out_dev, b.n * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CUDA_OK(cudaMemcpyAsync(b.out_user + first, b.out_dev + first, count * sizeof(double), cudaMemcpyDeviceToHost, st));
   }
   CUDA_OK(cudaStreamSynchronize(st));
   float ms = 0.f;

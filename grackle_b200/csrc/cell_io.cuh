@@ -177,6 +177,12 @@ __device__ __forceinline__ void coop_fetch(const double *table, int my_off, doub
 // and of the next pass - are in flight together: as two separate coop_fetch loops the compiler
 // serialised the second one (ncu, round 2: 13 fully exposed L2 round trips per subcycle, 17 % of
 // the kernel's time).
+// GRB_SKIP_SEG2 = 1: cells that will not read segment 2 this subcycle pass a negative offset and
+// their lanes issue no load (fewer 128-byte lines per instruction).  MEASURED slower (B200, C4:
+// 38.45 against 39.41 Mcell/s): the predicate costs more issue slots than the lines save.
+#ifndef GRB_SKIP_SEG2
+#define GRB_SKIP_SEG2 0
+#endif
 #ifndef GRB_FETCH_BATCH
 #define GRB_FETCH_BATCH 2      /* passes whose loads are issued before the first of them is consumed */
 #endif
@@ -209,10 +215,16 @@ __device__ __forceinline__ void coop_fetch2(const double *table1, int my_off1, d
       for (int k = 0; k < PER1; k++)
         if ((k + 1) * G <= NC1 || g + k * G < NC1)
           p1[b][k] = __ldg(reinterpret_cast<const double2 *>(src1 + GRB_OFF(off1) + 16 * k * G));
+      // off2 < 0: this cell does not read segment 2 this subcycle (k13_martin is only evaluated for
+      // 500 K <= T < 1e6 K; idle lanes): its lanes issue no load, so the instruction touches fewer
+      // 128-byte lines - the kernel is bound by the wavefronts of the load/store data pipe
 #pragma unroll
       for (int k = 0; k < PER2; k++)
-        if ((k + 1) * G <= NC2 || g + k * G < NC2)
-          p2[b][k] = __ldg(reinterpret_cast<const double2 *>(src2 + GRB_OFF(off2) + 16 * k * G));
+        if ((k + 1) * G <= NC2 || g + k * G < NC2) {
+          p2[b][k] = make_double2(0.0, 0.0);
+          if (!GRB_SKIP_SEG2 || off2 >= 0)
+            p2[b][k] = __ldg(reinterpret_cast<const double2 *>(src2 + GRB_OFF(off2) + 16 * k * G));
+        }
     }
 #pragma unroll
     for (int b = 0; b < NB; b++) {

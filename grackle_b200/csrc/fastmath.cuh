@@ -236,12 +236,34 @@ GRB_FM_FN double dexp10(double x)
 // ---------------------------------------------------------------------------------------
 #define GRB_FM_TABLE_DOUBLES 320
 
+// Size of the 2^(j/N) table of exp / exp10 (build knob; 64 is what ships).  A lookup at a per-lane
+// index costs one shared-memory wavefront per distinct entry sharing a bank: 3.8 - 4.8 wavefronts
+// per 64-entry lookup where 2 is the minimum for 32 eight-byte reads, and ncu (round 2) has the
+// load/store data pipe at 86 % of its peak.  N = 16 makes the table one 128-byte bank row - every
+// lookup conflict-free - for a degree-5 instead of degree-3 tail polynomial (two more FMAs per
+// call).  MEASURED (B200, C4, 16 Mi cells): 39.41 Mcell/s with N = 64, 38.38 with N = 16: the two
+// FMAs on the dependent chain cost more than the wavefronts save.  Likewise GRB_FM_LOG_NOTABLE
+// (division-based log core, no 16-byte lookup, +10 FP64 instructions): 37.23 Mcell/s.
+#ifndef GRB_FM_EXP_N
+#define GRB_FM_EXP_N 64
+#endif
+#define GRB_FM_EXP_SHIFT (GRB_FM_EXP_N == 64 ? 6 : (GRB_FM_EXP_N == 32 ? 5 : 4))
+static_assert(GRB_FM_EXP_N == 64 || GRB_FM_EXP_N == 32 || GRB_FM_EXP_N == 16, "exp table entries");
+
+
 // [0] -1/2 [1] 1/3 [2] -1/4 [3] 1/5 [4] -1/6 ; [5] 1/2 [6] 1/6 [7] 1/24 [8] 1/120
 // [9] 64/ln2 [10] (ln2/64)_hi [11] (ln2/64)_lo [12] 64 log2(10) [13] (log10(2)/64)_hi [14] (log10(2)/64)_lo
-GRB_FM_CONST double FM_T[15] = {
+// (the 64-entry values; a table of N entries scales [9], [12] by N/64 and [10], [11], [13], [14] by 64/N - powers of
+// two, exact - see FM_X below)   [15] 1/720 [16] 1/5040
+GRB_FM_CONST double FM_T[17] = {
     -0.5, 1.0 / 3.0, -0.25, 0.2, -1.0 / 6.0, 0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0,
     92.33248261689366, 0.010830424696249145, 3.623510646634843e-19,
-    212.60339807279118, 0.004703593682249706, -4.380825199664329e-20};
+    212.60339807279118, 0.004703593682249706, -4.380825199664329e-20, 1.0 / 720.0, 1.0 / 5040.0};
+// [0] N/ln2 [1] (ln2/N)_hi [2] (ln2/N)_lo [3] N log2(10) [4] (log10(2)/N)_hi [5] (log10(2)/N)_lo
+#define GRB_FM_XS (64.0 / GRB_FM_EXP_N)
+GRB_FM_CONST double FM_X[6] = {
+    92.33248261689366 / GRB_FM_XS, 0.010830424696249145 * GRB_FM_XS, 3.623510646634843e-19 * GRB_FM_XS,
+    212.60339807279118 / GRB_FM_XS, 0.004703593682249706 * GRB_FM_XS, -4.380825199664329e-20 * GRB_FM_XS};
 
 // host side: fill the table (long double libm)
 static inline void fm_fill_tables(double *tab)
@@ -252,7 +274,8 @@ static inline void fm_fill_tables(double *tab)
     tab[2 * i] = inv;
     tab[2 * i + 1] = (double)(-logl((long double)inv));
   }
-  for (int j = 0; j < 64; j++) tab[256 + j] = (double)exp2l((long double)j / 64.0L);
+  for (int j = 0; j < 64; j++) tab[256 + j] = 0.0;
+  for (int j = 0; j < GRB_FM_EXP_N; j++) tab[256 + j] = (double)exp2l((long double)j / (long double)GRB_FM_EXP_N);
 }
 
 GRB_FM_HD double fm_ldtab(const double *p) { return *p; }
@@ -265,8 +288,40 @@ GRB_FM_HD bool fm_den_special(double b) { return (unsigned)((fm_hi(b) & 0x7ff000
 
 // The unchecked cores.  Polynomials in Estrin form: the degree-4 / degree-3 tails are two
 // dependent steps deep instead of four / three (same coefficients, ~2 ulp as before).
+// GRB_FM_LOG_NOTABLE: the division-based core (no shared-memory lookup: the (1/c, ln c) pair read at
+// a per-lane index is a 16-byte access that costs ~10 wavefronts for 32 lanes; 21 FP64 instructions
+// and a MUFU instead of 11 and the lookup)
+GRB_FM_HD double dlog_nc_div(double x)
+{
+  int hi = fm_hi(x);
+  int e = (hi >> 20) - 1023;
+  hi = (hi & 0x000fffff) | 0x3ff00000;
+  const int up = (hi >= 0x3ff6a09f) ? 1 : 0;               // m in [sqrt(1/2), sqrt(2))
+  hi -= up << 20; e += up;
+  const double m = fm_make(hi, fm_lo(x));
+  const double f = (m - 1.0) * drcp(m + 1.0);
+  const double s = f * f;
+  // atanh(f)/f - 1 = s (c0 + c1 s + ... + c8 s^8), Estrin
+  const double s2 = s * s, s4 = s2 * s2;
+  const double a01 = fma(FM_LOG_C[1], s, FM_LOG_C[0]);
+  const double a23 = fma(FM_LOG_C[3], s, FM_LOG_C[2]);
+  const double a45 = fma(FM_LOG_C[5], s, FM_LOG_C[4]);
+  const double a67 = fma(FM_LOG_C[7], s, FM_LOG_C[6]);
+  const double b03 = fma(a23, s2, a01);
+  const double b47 = fma(a67, s2, a45);
+  const double p = fma(fma(FM_LOG_C[8], s4, b47), s4, b03);
+  const double f2 = f + f;
+  const double lm = fma(f2, p * s, f2);                   // log(m) = 2 atanh(f)
+  const double de = (double)e;
+  return fma(de, FM_K[0], fma(de, FM_K[1], lm));
+}
+
 GRB_FM_HD double dlog_nc(double x, const double *tab)
 {
+#ifdef GRB_FM_LOG_NOTABLE
+  (void)tab;
+  return dlog_nc_div(x);
+#endif
   const int hi = fm_hi(x);
   const int i = (hi >> 13) & 0x7f;
   const double m = fm_make((hi & 0x000fffff) | 0x3ff00000, fm_lo(x));     // [1, 2)
@@ -285,37 +340,42 @@ GRB_FM_HD double dlog_nc(double x, const double *tab)
   return big + fma(de, FM_K[1], sm);
 }
 
-// 2^n * T * exp(r), |r| <= ln2/128
+// 2^n * T * exp(r), |r| <= ln2 / (2 N)
 GRB_FM_HD double fm_exp_tab_core(double r, int kk, const double *tab)
 {
-  const double T = fm_ldtab(tab + 256 + (kk & 63));
-  // exp(r) - 1 = r + r^2 (c5 + c6 r + c7 r^2 + c8 r^3)
+  const double T = fm_ldtab(tab + 256 + (kk & (GRB_FM_EXP_N - 1)));
+  // exp(r) - 1 = r + r^2 (1/2 + r/6 + r^2/24 + r^3/120 [+ r^4/720 + r^5/5040])
   const double r2 = r * r;
   const double t0 = fma(FM_T[6], r, FM_T[5]);
   const double t1 = fma(FM_T[8], r, FM_T[7]);
+#if GRB_FM_EXP_N == 64
   const double p = fma(t1, r2, t0);
+#else
+  const double t2 = fma(FM_T[16], r, FM_T[15]);
+  const double p = fma(fma(t2, r2, t1), r2, t0);
+#endif
   const double em1 = fma(r2, p, r);
   const double v = fma(T, em1, T);
-  return fm_make(fm_hi(v) + ((kk >> 6) << 20), fm_lo(v));
+  return fm_make(fm_hi(v) + ((kk >> GRB_FM_EXP_SHIFT) << 20), fm_lo(v));
 }
 
 GRB_FM_HD double dexp_nc(double x, const double *tab)
 {
-  const double t = fma(x, FM_T[9], FM_K[3]);
+  const double t = fma(x, FM_X[0], FM_K[3]);
   const int kk = fm_lo(t);
   const double nf = t - FM_K[3];
-  double r = fma(nf, -FM_T[10], x);
-  r = fma(nf, -FM_T[11], r);
+  double r = fma(nf, -FM_X[1], x);
+  r = fma(nf, -FM_X[2], r);
   return fm_exp_tab_core(r, kk, tab);
 }
 
 GRB_FM_HD double dexp10_nc(double x, const double *tab)
 {
-  const double t = fma(x, FM_T[12], FM_K[3]);
+  const double t = fma(x, FM_X[3], FM_K[3]);
   const int kk = fm_lo(t);
   const double nf = t - FM_K[3];
-  double r = fma(nf, -FM_T[13], x);     // decades left over
-  r = fma(nf, -FM_T[14], r);
+  double r = fma(nf, -FM_X[4], x);     // decades left over
+  r = fma(nf, -FM_X[5], r);
   const double y = fma(r, FM_K[8], r * FM_K[7]);
   return fm_exp_tab_core(y, kk, tab);
 }

@@ -63,12 +63,18 @@ struct GrCloudyDev {
   int fast;                // 1 when the fields below are set
   int heat_in_ch;          // the pairs carry a heating value
   int fdim[2];             // n_H, T points
-  const double *ch;        // [n_H][T][2] = (cooling, heating)
+  const double *ch;        // [n_H][T][GRB_CLOUDY_ENTRY]: (cooling, heating) of the point [and of its right-hand T neighbour]
   const double *cmb;       // [n_H] cooling at T_CMB
   const double *ax[2];     // per axis [points][2] = (stored axis value p_i, 1 / (p_{i+1} - p_i)): the stored
                            // axes are only nominally uniform (CloudyData_noUVB.h5: 10^1.05 written as 11.22018)
   double par0[2], inv_dpar[2], fdpar[2];   // axis origin, 1/spacing, spacing (index computation only)
 };
+
+// doubles per grid point of the solve-kernel Cloudy plane: 4 = the point and its right-hand T
+// neighbour (two 256-bit loads per lookup), 2 = the point alone (four 128-bit loads; build knob)
+#ifndef GRB_CLOUDY_ENTRY
+#define GRB_CLOUDY_ENTRY 4
+#endif
 
 // the 15 density-like fields + energy, in the order the kernels index them
 enum {

@@ -135,6 +135,12 @@ __device__ inline double cloudy_lookup(const GrCloudyDev &c, const double *data,
 //     10^1.05 as 11.22018 - and the real-table parity test of round 2 showed a 4e-6 error in the
 //     cooling rate from it.)
 //   * the CMB-floor term (cooling at T_CMB, cell-invariant along T) read from a per-row array.
+// 256-bit read-only load (32-byte aligned address)
+__device__ __forceinline__ void ld_nc_v4(const double *p, double &a, double &b, double &c, double &d)
+{
+  asm("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+
 template <class M>
 __device__ __forceinline__ double cloudy_edot_fast_m(M &m, const GrParams &P, const GrCloudyDev &c, double rhoH,
                                                      double metallicity, double logtem, int icmbTfloor, int iZscale)
@@ -149,8 +155,20 @@ __device__ __forceinline__ double cloudy_edot_fast_m(M &m, const GrParams &P, co
   const double2 a2 = __ldg(reinterpret_cast<const double2 *>(c.ax[1]) + (i2 - 1));
   const double w1 = (log_n_h - a1.x) * a1.y;
   const double w2 = (log10tem - a2.x) * a2.y;
+#if GRB_CLOUDY_ENTRY == 4
+  // one 32-byte entry per grid point: (cooling, heating) of the point AND of its right-hand T
+  // neighbour, so the four corners are two 256-bit loads (sm_100a LDG.E.256) instead of four 128-bit
+  // ones.  Every lane reads its own (n_H, T) point - 32 different lines per instruction - and both
+  // kernels that call this are bound by the wavefronts of the load/store data pipe (ncu round 2:
+  // 86 % / 90 % of peak; these gathers were 25 tag requests each, a quarter of the kernel's total).
+  const double *g = c.ch + 4 * ((i1 - 1) * c.fdim[1] + (i2 - 1));
+  double2 v00, v01, v10, v11;
+  ld_nc_v4(g, v00.x, v00.y, v01.x, v01.y);
+  ld_nc_v4(g + 4 * c.fdim[1], v10.x, v10.y, v11.x, v11.y);
+#else
   const double2 *g = reinterpret_cast<const double2 *>(c.ch) + ((i1 - 1) * c.fdim[1] + (i2 - 1));
   const double2 v00 = __ldg(g), v01 = __ldg(g + 1), v10 = __ldg(g + c.fdim[1]), v11 = __ldg(g + c.fdim[1] + 1);
+#endif
   const bool floor_on = (icmbTfloor == 1) && ((log10tem - P.log10_tcmb) < 2.0);
   double m0 = 0.0, m1 = 0.0;
   if (floor_on) { m0 = ld(c.cmb + i1 - 1); m1 = ld(c.cmb + i1); }

@@ -326,9 +326,13 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
       }
     }
     // stage 2 (warp): cooling rows and the k13dd coefficients -> slots
-    if (PC > 1 && P.ithreebody == 0)
-      coop_fetch2<G, NCA, NCOOL * 16, 14, NCHEM * 16, CS>(P.cool, offA, tdefA, P.chem + 2 * C_K13DD0, offB, tb.tdef,
+    if (PC > 1 && P.ithreebody == 0) {
+      // the k13dd coefficients are read by k13_martin only (network.cuh: 500 K <= T < 1e6 K)
+      const bool want_k13 = active && th.tgas >= 500.0 && th.tgas < 1.0e6;
+      coop_fetch2<G, NCA, NCOOL * 16, 14, NCHEM * 16, CS>(P.cool, offA, tdefA, P.chem + 2 * C_K13DD0,
+                                                          (GRB_SKIP_SEG2 && !want_k13) ? -1 : offB, tb.tdef,
                                                           warp_slots + SLA_COOL * CS);
+    }
     else if (PC > 1 || anydust) coop_fetch<G, NCA, NCOOL * 16, CS>(P.cool, offA, tdefA, warp_slots + SLA_COOL * CS);
     else if (PC == 1) coop_fetch<G, L_BREM + 1, NCOOL * 16, CS>(P.cool, offA, tdefA, warp_slots + SLA_COOL * CS);
     __syncwarp();
