@@ -6,6 +6,8 @@ reference's c_example / cxx_example binaries RUN on the CUDA path (the table the
 path is the synthetic HM2012-schema file).
 """
 import os
+
+import numpy as np
 import shutil
 import subprocess
 
@@ -66,12 +68,16 @@ def test_reference_example_runs_on_the_cuda_path(tmp_path, synth_table, name):
     cwd.mkdir(parents=True)
     run = subprocess.run([exe], cwd=str(cwd), capture_output=True, text=True, timeout=300)
     assert run.returncode == 0, run.stdout[-500:] + run.stderr[-500:]
-    out = run.stdout
-    for key in ("cooling_time", "temperature", "pressure", "gamma"):
-        assert key in out, out
+    # the examples report on stderr: "Cooling time = ... s.", "Temperature = ... K.", "Pressure = ...",
+    # "gamma = ...", "dust_temperature = ... K." (c_example.c:197-244, cxx_example.C:204-251)
+    out = run.stdout + run.stderr
     vals = {}
     for ln in out.splitlines():
-        for key in ("temperature", "gamma"):
+        for key in ("Cooling time", "Temperature", "Pressure", "gamma", "dust_temperature"):
             if ln.strip().startswith(key + " ="):
-                vals[key] = float(ln.split("=")[1].split()[0])
-    assert 1.0 < vals["gamma"] < 1.7 and vals["temperature"] > 1.0, vals
+                vals[key] = float(ln.split("=")[1].split()[0].rstrip("."))
+    assert set(vals) == {"Cooling time", "Temperature", "Pressure", "gamma", "dust_temperature"}, out[-1500:]
+    assert all(np.isfinite(v) for v in vals.values()), vals
+    # the example's cell: 1 cm^-3 gas at ~1000 K after one solve step, dust_chemistry = 1
+    assert 1.0 < vals["gamma"] < 1.7 and 1.0 < vals["Temperature"] < 1e5 and vals["Pressure"] > 0.0, vals
+    assert vals["Cooling time"] != 0.0 and 2.7 < vals["dust_temperature"] < 1e3, vals
