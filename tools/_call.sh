@@ -1,6 +1,8 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_multi_device.py -m gpu -x -q 2>&1 | tail -3
-python tools/multi_device_probe.py 32 B > gpurun_out/r2z_multi_device.txt 2>&1
-python tools/multi_device_probe.py 32 C >> gpurun_out/r2z_multi_device.txt 2>&1
-cat gpurun_out/r2z_multi_device.txt | cut -c1-300
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2aa_smoke.txt 2>&1; tail -3 gpurun_out/r2aa_smoke.txt | cut -c1-300
+echo "== general instantiation forced, Set B, 16 Mi cells" > gpurun_out/r2aa_general.txt
+python tools/bench_configs.py 24 B general 2>&1 | grep -E "Mcell|rror" >> gpurun_out/r2aa_general.txt
+echo "== default (compact) instantiations" >> gpurun_out/r2aa_general.txt
+python tools/bench_configs.py 24 B 2>&1 | grep -E "Mcell|rror" >> gpurun_out/r2aa_general.txt
+cat gpurun_out/r2aa_general.txt
