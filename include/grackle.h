@@ -201,6 +201,14 @@ int grb200_set_devices(chemistry_data *my_chemistry, chemistry_data_storage *my_
 /* number of device contexts of this storage (1 unless grb200_set_devices raised it; 0: none) */
 int grb200_get_devices(chemistry_data_storage *my_rates);
 
+/* Concurrent callers.  The reference's local_* entry points are re-entrant (no global state: that
+ * is what they exist for, src/clib/grackle.h:60-117), and patch-based simulation codes call them
+ * from several host threads at once, each on its own grid.  Calls that arrive while this storage's device context is
+ * busy run on up to n - 1 further contexts on the same GPU (made on first need: own streams, staging
+ * buffers, table copies), so one caller's copies overlap another's kernel; beyond n they queue.
+ * Default 3; n = 1 serialises all calls on a storage, as does a caller-owned stream (grb200_set_stream). */
+int grb200_set_caller_contexts(chemistry_data_storage *my_rates, int n);
+
 /* calculate_dust_temperature for callers that must not trigger a device or host allocation (code
    under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO
    counterpart in the reference.
