@@ -1,6 +1,6 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_pipeline.py tests/test_gpu_multi_device.py tests/test_zz_no_alloc.py tests/test_gpu_flat_api.py -m gpu -x -q 2>&1 | tail -4
-python tools/concurrent_callers_probe.py 8 20 > gpurun_out/r2ac_concurrent.txt 2>&1
-python tools/concurrent_callers_probe.py 16 18 >> gpurun_out/r2ac_concurrent.txt 2>&1
-cat gpurun_out/r2ac_concurrent.txt | cut -c1-250
+( time timeout 1800 python -m pytest tests -m gpu -x -q -rs ) > gpurun_out/r2ad_pytest.log 2>&1; tail -5 gpurun_out/r2ad_pytest.log
+python tools/multi_device_probe.py 32 B > gpurun_out/r2ad_multi_device.txt 2>&1
+python tools/multi_device_probe.py 32 C >> gpurun_out/r2ad_multi_device.txt 2>&1
+cat gpurun_out/r2ad_multi_device.txt | cut -c1-300
