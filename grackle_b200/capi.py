@@ -179,6 +179,8 @@ def load_product():
     lib.grb200_set_devices.restype = C.c_int
     lib.grb200_get_devices.argtypes = [C.POINTER(ChemistryStorage)]
     lib.grb200_get_devices.restype = C.c_int
+    lib.grb200_set_cell_ordering.argtypes = [C.c_longlong, C.c_longlong]
+    lib.grb200_set_cell_ordering.restype = None
     lib.grb200_set_caller_contexts.argtypes = [C.POINTER(ChemistryStorage), C.c_int]
     lib.grb200_set_caller_contexts.restype = C.c_int
     return lib

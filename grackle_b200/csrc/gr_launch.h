@@ -20,5 +20,8 @@ void grb_launch_solve(const GrParams &P, int blocks, cudaStream_t st);
 int grb_solve_variant_for(const GrParams &P);   // 0 general, 1 lean, 2 lean + H2-on-dust + UVB self-shielding
 extern int grb_solve_variant;       // 0 = choose per call, 1 = always the general instantiation
 int grb_solve_max_blocks_per_sm(int pc);
+// cost-ordered work queue (order.cu)
+size_t grb_cost_order_bytes(long long n);
+const unsigned *grb_build_cost_order(const GrParams &P, void *scratch, size_t scratch_bytes, cudaStream_t st);
 double grb_launch_fp64_peak(double *sink, int blocks, int iters, cudaStream_t st);
 #endif

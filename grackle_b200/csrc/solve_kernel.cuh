@@ -259,7 +259,9 @@ __device__ __forceinline__ void solve_cells(const GrParams &P)
         const long long t = (long long)(base + __popc(need & ((1u << lane) - 1)));
         if (t < P.nactive) {
           int ci, cj, ck;
-          const size_t x = cell_index(P, t, ci, cj, ck);
+          // (the chunk-streaming path needs queue order = memory order: it runs without a permutation)
+          const long long cell_t = (!PIPE && P.perm != nullptr) ? (long long)__ldg(P.perm + t) : t;
+          const size_t x = cell_index(P, cell_t, ci, cj, ck);
           cell_x = x;
           bool ready = true;
           if (PIPE) {

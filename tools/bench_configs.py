@@ -17,6 +17,8 @@ set_name = sys.argv[2] if len(sys.argv) > 2 else "B"
 lib = capi.load_product()
 if len(sys.argv) > 3 and sys.argv[3] == "general":
     lib.grb200_set_solve_variant(1)      # force the general instantiation
+if os.environ.get("ORDERING") == "0":
+    lib.grb200_set_cell_ordering(1, 0)           # plain queue order (the cost-ordered queue of order.cu off)
 table = synth_tables.ensure()
 dev = torch.device("cuda", 0)
 for name in os.environ.get("CONFIGS", "C1,C2,C3,C4").split(","):
