@@ -253,7 +253,7 @@ def test_concurrent_callers_get_their_own_context(product_lib, synth_table, pipe
 
 @pytest.mark.parametrize("name", ["C1", "C2", "C3", "C4"])
 def test_cost_ordered_queue_changes_nothing_but_the_order(product_lib, synth_table, name):
-    """order.cu: calls of 2^15 ... 2^28 active cells walk the work queue densest cell first (removes the
+    """order.cu: calls of 2^15 ... 2^25 active cells walk the work queue densest cell first (removes the
     tail of a launch).  Same cells, same arithmetic: results and diagnostics are bitwise those of the
     plain queue, with ghost zones, on host and on device arrays."""
     import torch
@@ -263,7 +263,7 @@ def test_cost_ordered_queue_changes_nothing_but_the_order(product_lib, synth_tab
     try:
         product_lib.grb200_set_cell_ordering(1, 0)                  # off
         ref, st0 = _solve(cp, fields, dims, dt, start=start, end=end)
-        product_lib.grb200_set_cell_ordering(1 << 15, 1 << 28)      # the default
+        product_lib.grb200_set_cell_ordering(1 << 15, 1 << 25)      # the default
         got, st1 = _solve(cp, fields, dims, dt, start=start, end=end)
         _same(ref, got)
         assert (st0.cells, st0.subcycles_sum, st0.subcycles_max, st0.cells_hit_itmax) == \
@@ -275,7 +275,7 @@ def test_cost_ordered_queue_changes_nothing_but_the_order(product_lib, synth_tab
         b, _ = _solve(cp, small, [777], dt)
         _same(a, b)
         # device-resident arrays
-        product_lib.grb200_set_cell_ordering(1 << 15, 1 << 28)
+        product_lib.grb200_set_cell_ordering(1 << 15, 1 << 25)
         dev = {k: torch.from_numpy(v).cuda() for k, v in fields.items()}
         g = capi.Grid(dims, start=start, end=end)
         for k, v in dev.items():
@@ -284,5 +284,5 @@ def test_cost_ordered_queue_changes_nothing_but_the_order(product_lib, synth_tab
         torch.cuda.synchronize()
         _same(ref, {k: dev[k].cpu().numpy() for k in ref})
     finally:
-        product_lib.grb200_set_cell_ordering(1 << 15, 1 << 28)
+        product_lib.grb200_set_cell_ordering(1 << 15, 1 << 25)
         cp.free()
