@@ -141,9 +141,14 @@ __device__ __forceinline__ void load_extras(const GrParams &P, size_t x, Cell &c
 // general pc = 0/1 kernels, 8 for the general / dust + shielding kernels of the H2 networks.
 // Round 2 (column-major slots, per-cell state in shared memory, fewer instructions): the compact
 // kernels run fastest WITHOUT grouping (C4: 37.8 Mcell/s against 34.8 with groups of 2) - the
-// barrier wait now costs more than the instruction-cache misses it avoids.
+// barrier wait now costs more than the instruction-cache misses it avoids.  Re-measured at the end
+// of round 2 (8 Mi cells, Set B, groups of 16 / 8 / 4 / 2 / 1 warps): general pc = 0 kernel - / - / 35.0 / 36.2 /
+// 38.1 and general pc = 1 - / - / 74.2 / 80.8 / 88.7 Mcell/s (no grouping now); general pc = 2 19.3 / 19.7 / 16.3 /
+// 13.8 / 14.1, general pc = 3 22.7 / 25.2 / 24.6 / 23.6 / 24.0, dust + shielding pc = 2 21.4 / 23.1 / 20.7 / 18.0 /
+// 19.2 (groups of 8 stay).  The dust_chemistry kernel (VAR_DUST_ALL) prefers no grouping on uniform
+// inputs (Set H: 11.6 against 10.6 Mcell/s) and groups of 8 on the broad Set B (23.2 against 22.4): 8 ships.
 #ifndef GRB_GROUP_WARPS
-#define GRB_GROUP_WARPS 4
+#define GRB_GROUP_WARPS 1
 #endif
 #ifndef GRB_GROUP_WARPS_LEAN
 #define GRB_GROUP_WARPS_LEAN 1
@@ -154,7 +159,11 @@ __device__ __forceinline__ void load_extras(const GrParams &P, size_t x, Cell &c
 #ifndef GRB_GROUP_WARPS_BIG
 #define GRB_GROUP_WARPS_BIG 8
 #endif
-static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS_BIG) == 0, "CTA must be whole lockstep groups");
+#ifndef GRB_GROUP_WARPS_DUSTALL
+#define GRB_GROUP_WARPS_DUSTALL 8
+#endif
+static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS_BIG) == 0 && GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS_DUSTALL) == 0,
+              "CTA must be whole lockstep groups");
 static_assert(GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS) == 0 && GRB_SOLVE_THREADS % (32 * GRB_GROUP_WARPS_LEAN) == 0,
               "CTA must be whole lockstep groups");
 static_assert((GRB_GROUP_WARPS == 1 || GRB_SOLVE_THREADS / (32 * GRB_GROUP_WARPS) <= 15) &&
@@ -408,7 +417,7 @@ template <int PC, int VAR>
 __host__ __device__ constexpr int solve_group_warps()
 {
   return (VAR == VAR_LEAN) ? ((PC <= 1) ? GRB_GROUP_WARPS_LEAN_SMALL : GRB_GROUP_WARPS_LEAN)
-                           : ((PC <= 1) ? GRB_GROUP_WARPS : GRB_GROUP_WARPS_BIG);
+                           : ((PC <= 1) ? GRB_GROUP_WARPS : (VAR == VAR_DUST_ALL ? GRB_GROUP_WARPS_DUSTALL : GRB_GROUP_WARPS_BIG));
 }
 
 template <int PC, int VAR, bool PIPE>
