@@ -178,7 +178,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     const double gaHI = cv(L_GAHI), gaH2 = cv(L_GAH2), gaHe = cv(L_GAHE), gaHp = cv(L_GAHP);
     const double gael = cv(L_GAEL), h2lte = cv(L_H2LTE);
     double fudge = 1.0;
-    if (GRB_RARE(P.ih2optical == 1)) {
+    if (P.ih2optical == 1) {
       fudge = POW_POS(0.76 * c.d * dom / 8.e9, -0.45);
       fudge = dmin(fudge, 1.0);
     }
@@ -191,7 +191,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
       if (f.bad) q = ddiv_s(num, 1.0 + ddiv_s(gphdl1, galdl));
       edot = edot - q * (0.5 * dom_inv);
     }
-    if (GRB_RARE(P.iciecool == 1 && c.d * dom > 1e10)) {
+    if (P.iciecool == 1 && c.d * dom > 1e10) {
       const double cieco = cv(L_CIECO);
       double tau = POW_POS((c.d / 2e16) * dom, 2.8);
       tau = dmax(tau, 1.e-5);
@@ -217,7 +217,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
   double myisrf = 0.0;
   if (anydust || (P.igammah > 1)) myisrf = (P.iisrffield > 0) ? c.isrf : P.isrf;
 
-  if (GRB_RARE(anydust)) {    // gas-grain heat transfer and T_dust (:726-753)
+  if (anydust) {    // gas-grain heat transfer and T_dust (:726-753)
     const double gasgr = cv(L_GASGR);
     const double gasgr_tdust = P.fgr * gasgr * P.coolunit / GRB_MASS_H;
     th.tdust = dust_temperature(P, th.tgas, mynh, gasgr_tdust, P.gamma_isrfa, myisrf, P.comp2);
@@ -226,11 +226,11 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
 
   if (PC > 0) {     // UVB photo-heating with optional self-shielding (:758-913)
     double fH = 1.0, fHe = 1.0;
-    if (GRB_RARE(P.iradshield >= 1 && !(P.k24 < GRB_TINY8))) {
+    if (P.iradshield >= 1 && !(P.k24 < GRB_TINY8)) {
       const double nSSh = P.ssh_sig_hi * POW_POS(th.tgas / 1.0e4, 0.17) * P.ssh_k24;
       fH = rahmati_f(P, (c.HI + c.HII) * dom / nSSh);
     }
-    if (GRB_RARE(P.iradshield >= 2 && !(P.k26 < GRB_TINY8))) {
+    if (P.iradshield >= 2 && !(P.k26 < GRB_TINY8)) {
       const double nSSh_he = P.ssh_sig_hei * POW_POS(th.tgas / 1.0e4, 0.17) * P.ssh_k26;
       fHe = rahmati_f(P, 0.25 * (c.HeI + c.HeII + c.HeIII) * dom / nSSh_he);
     }
@@ -253,7 +253,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     th.myde = dmax(myde, 0.0);
   }
 
-  if (GRB_RARE(P.igammah > 0)) {   // photo-electric heating by dust (:951-1001)
+  if (P.igammah > 0) {   // photo-electric heating by dust (:951-1001)
     double geff;
     if (P.igammah == 1) {
       geff = (th.tgas > 2.e4) ? 0.0 : P.gammaha;
@@ -268,7 +268,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     edot = edot + geff * th.rhoH * dom_inv * th.dust2gas / P.fgr;
   }
 
-  if (GRB_RARE((P.idustall > 0) || (P.idustrec > 0))) {   // grain recombination cooling (:1005-1023)
+  if ((P.idustall > 0) || (P.idustrec > 0)) {   // grain recombination cooling (:1005-1023)
     const double regr = cv(L_REGR);
     const double grbeta = 0.74 / POW_POS(th.tgas, 0.068);
     edot = edot - regr * POW_POS(myisrf * dom_inv / th.myde, grbeta) * th.myde * th.rhoH * th.dust2gas / P.fgr;
@@ -282,7 +282,7 @@ __device__ inline void cool_sums(const GrParams &P, const Cell &c, double logtem
     edot = edot + (double)P.ipiht * c.photogamma / P.coolunit * c.HI / dom;
 
   if (P.imcool == 1) {   // Cloudy metal cooling (:1069-1097)
-    if (GRB_USUAL(P.clnew == 1)) edot = edot + cloudy_edot(P, P.met, th.rhoH, th.metallicity, logtem, P.icmbTfloor, 1);
+    if (P.clnew == 1) edot = edot + cloudy_edot(P, P.met, th.rhoH, th.metallicity, logtem, P.icmbTfloor, 1);
     else edot = edot + cloudy_old_edot(P, P.met, c.d, c.de, th.rhoH, th.metallicity, logtem);
   }
 

@@ -146,7 +146,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
   }
 
   // H2 formation on grains: bilinear in (ln T, ln T_dust) (:1327-1378)
-  if (GRB_RARE(anydust)) {
+  if (anydust) {
     if (th.tdust > P.dtemend) {
       RS(h2dust) = GRB_TINY8;
     } else {
@@ -167,7 +167,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
 
   if (PC > 1 && (!FOLD || k31_per_cell<PC>(P))) {     // H2 self-shielding, Wolcott-Green & Haiman (2019) (:1397-1490)
     double k31s = (P.iradtrans == 0) ? P.k31 : P.k31 + c.kdissH2I;
-    if (GRB_RARE(P.iH2shield > 0)) {
+    if (P.iH2shield > 0) {
       double l_H2shield;
       if (P.iH2shield == 1) {
         double divrho = GRB_TINY;
@@ -202,7 +202,7 @@ __device__ inline void lookup_rates(const GrParams &P, const Cell &c, const Ther
     RS(k31s) = k31s;
   }
 
-  if (GRB_RARE(uvb_shielded(P))) {   // UVB self-shielding (:1492-1676)
+  if (uvb_shielded(P)) {   // UVB self-shielding (:1492-1676)
     const double tfac = POW_POS(th.tgas / 1.0e4, 0.17);
     double nratio = (c.HI + c.HII);
     if (PC > 1) {

@@ -17,9 +17,6 @@ namespace grb {
 #define GRB_MASS_H 1.67262171e-24
 #define GRB_SIGMA_SB 5.670373e-5
 #define GRB_TINY 1.0e-20
-// optional physics of the general kernels: keep its code out of the straight-line path
-#define GRB_RARE(c) __builtin_expect(!!(c), 0)
-#define GRB_USUAL(c) __builtin_expect(!!(c), 1)
 #define GRB_TINY8 1.0e-40
 #define GRB_HUGE8 1.0e40
 #define GRB_MU_METAL 16.0
@@ -204,7 +201,7 @@ __device__ __forceinline__ double cloudy_edot_fast(const GrParams &P, const GrCl
 __device__ inline double cloudy_edot(const GrParams &P, const GrCloudyDev &c, double rhoH,
                                      double metallicity, double logtem, int icmbTfloor, int iZscale)
 {
-  if (GRB_USUAL(c.fast == 1)) return cloudy_edot_fast(P, c, rhoH, metallicity, logtem, icmbTfloor, iZscale);
+  if (c.fast == 1) return cloudy_edot_fast(P, c, rhoH, metallicity, logtem, icmbTfloor, iZscale);
   const double log10_tCMB = P.log10_tcmb;
   const double log10tem = logtem * GRB_INV_LN10;
   const double log_n_h = DLOG10(rhoH * P.dom);
