@@ -1,8 +1,5 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-for v in lib lib_vrare; do
-  echo "== $v general"; GRB200_LIB=$PWD/grackle_b200/$v/libgrackle_b200.so python tools/bench_configs.py 23 B general 2>&1 | grep -E "Mcell|rror"
-  echo "== $v default"; GRB200_LIB=$PWD/grackle_b200/$v/libgrackle_b200.so python tools/bench_configs.py 23 B 2>&1 | grep -E "Mcell|rror"
-  GRB200_LIB=$PWD/grackle_b200/$v/libgrackle_b200.so CONFIGS=HARNESS python tools/bench_configs.py 21 H 2>&1 | grep -E "Mcell|rror"
-done > gpurun_out/r2ak_rare.txt 2>&1
-grep -v FATAL gpurun_out/r2ak_rare.txt
+for k in 0 2; do echo "== 2^24 key $k"; CONFIGS=C2,C3,C4 ORDER_KEY=$k python tools/bench_configs.py 24 B 2>&1 | grep -E "Mcell|rror"; done > gpurun_out/r2am_key.txt 2>&1
+echo "== 2^27 C4 key 2" >> gpurun_out/r2am_key.txt; ORDER_KEY=2 CONFIGS=C4 REPS=2 python tools/bench_configs.py 27 B 2>&1 | grep -E "Mcell|rror" >> gpurun_out/r2am_key.txt
+grep -v FATAL gpurun_out/r2am_key.txt
