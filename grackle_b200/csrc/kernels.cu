@@ -276,6 +276,7 @@ void grb_launch_cooling_time(const GrParams &P, cudaStream_t st)
   if (var == VAR_LEAN) k_cooling_time<PCV, VAR_LEAN><<<nb, GRB_CT_THREADS, 0, st>>>(P);           \
   else if (var == VAR_DUST_SHIELD) k_cooling_time<PCV, VAR_DUST_SHIELD><<<nb, GRB_CT_THREADS, 0, st>>>(P); \
   else if (var == VAR_DUST_ALL) k_cooling_time<PCV, VAR_DUST_ALL><<<nb, GRB_CT_THREADS, 0, st>>>(P);       \
+  else if (var == VAR_COMMON) k_cooling_time<PCV, VAR_COMMON><<<nb, GRB_CT_THREADS, 0, st>>>(P);           \
   else if (var == VAR_RANK45) k_cooling_time<PCV, VAR_RANK45><<<nb, GRB_CT_THREADS, 0, st>>>(P);            \
   else k_cooling_time<PCV, VAR_GENERAL><<<nb, GRB_CT_THREADS, 0, st>>>(P);
   DISPATCH_PC(P.ispecies, CALL)
@@ -298,12 +299,16 @@ int grb_solve_variant_for(const GrParams &P)
   if (P.iold45 != 0) return VAR_RANK45;
   if (grb_solve_variant != 0) return VAR_GENERAL;
   // "off" is <= 0 for every switch (unset options stay at -1, e.g. dust_recombination_cooling)
-  const bool off = P.idustfield <= 0 && P.ih2optical <= 0 && P.iciecool <= 0 && P.iH2shield <= 0 &&
-                   P.iradtrans <= 0 && P.iVheat <= 0 && P.iMheat <= 0 && P.iisrffield <= 0 && P.iH2shieldcustom <= 0;
-  const bool ok = off && (P.ispecies < 2 || P.ithreebody == 0) && (P.imcool == 0 || (P.clnew == 1 && P.met.fast == 1)) &&
-                  (P.ispecies > 0 || P.pri.fast == 1);
-  if (!ok) return VAR_GENERAL;
+  // no field-array inputs, new-style tables
+  const bool base = P.idustfield <= 0 && P.iradtrans <= 0 && P.iVheat <= 0 && P.iMheat <= 0 && P.iisrffield <= 0 &&
+                    P.iH2shieldcustom <= 0 && (P.imcool == 0 || (P.clnew == 1 && P.met.fast == 1)) &&
+                    (P.ispecies > 0 || P.pri.fast == 1);
+  if (!base) return VAR_GENERAL;
   const bool nodustall = P.idustall <= 0 && P.idustrec <= 0 && P.igammah <= 0;
+  const bool off = P.ih2optical <= 0 && P.iciecool <= 0 && P.iH2shield <= 0 && (P.ispecies < 2 || P.ithreebody == 0);
+  // the H2 networks with the collapse / galaxy-run switches on: Jeans-length H2 shielding, three-body rates,
+  // CIE cooling, optical-depth fudge (VAR_COMMON)
+  if (!off) return (nodustall && P.ispecies > 1 && (P.iH2shield <= 0 || P.iH2shield == 3)) ? VAR_COMMON : VAR_GENERAL;
   if (nodustall && P.idust <= 0 && P.iradshield <= 0) return VAR_LEAN;
   if (nodustall) return (P.ispecies > 0) ? VAR_DUST_SHIELD : VAR_GENERAL;
   // dust_chemistry = 1 with the settings it implies (initialize_chemistry_data.c:71-100), no UVB shielding

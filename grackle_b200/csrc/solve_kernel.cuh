@@ -458,6 +458,7 @@ inline void launch_solve_pc(const GrParams &P, int var, int blocks, cudaStream_t
   if (var == VAR_LEAN) GRB_LAUNCH_VAR(VAR_LEAN)
   else if (var == VAR_DUST_SHIELD) GRB_LAUNCH_VAR(VAR_DUST_SHIELD)
   else if (var == VAR_DUST_ALL) GRB_LAUNCH_VAR(VAR_DUST_ALL)
+  else if (var == VAR_COMMON) GRB_LAUNCH_VAR(VAR_COMMON)
   else if (var == VAR_RANK45) GRB_LAUNCH_VAR(VAR_RANK45)
   else GRB_LAUNCH_VAR(VAR_GENERAL)
 #undef GRB_LAUNCH_VAR

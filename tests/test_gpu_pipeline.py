@@ -286,3 +286,26 @@ def test_cost_ordered_queue_changes_nothing_but_the_order(product_lib, synth_tab
     finally:
         product_lib.grb200_set_cell_ordering(1 << 15, 1 << 25)
         cp.free()
+
+
+def test_chunked_common_variant(product_lib, synth_table, pipeline):
+    """the VAR_COMMON instantiation (three-body rates, CIE cooling, Jeans-length H2 shielding read at run
+    time) through the chunk-streaming path and on two slabs, against its own plain path and against the
+    general instantiation (same physics, different code: 1e-9 on the cells both builds of the oracle
+    reproduce is checked by test_gpu_variants; here: plain vs streaming vs dispatched, bitwise)"""
+    dims = [40, 24, 18]
+    over = dict(three_body_rate=4, cie_cooling=1, h2_optical_depth_approximation=1, H2_self_shielding=3,
+                self_shielding_method=3, h2_on_dust=1)
+    cp, fields, dt = _inputs("C4", synth_table, product_lib, int(np.prod(dims)), over)
+    try:
+        pipeline(0, 1)
+        ref, st0 = _solve(cp, fields, dims, dt)
+        pipeline(9, 1)
+        got, st1 = _solve(cp, fields, dims, dt)
+        _same(ref, got)
+        assert st0.subcycles_sum == st1.subcycles_sum
+        assert cp.lib.grb200_set_devices(C.byref(cp.chem), C.byref(cp.rates), 2, 2) == 1
+        got2, _ = _solve(cp, fields, dims, dt)
+        _same(ref, got2)
+    finally:
+        cp.free()

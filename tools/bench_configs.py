@@ -23,6 +23,9 @@ table = synth_tables.ensure()
 dev = torch.device("cuda", 0)
 for name in os.environ.get("CONFIGS", "C1,C2,C3,C4").split(","):
     params, dt, _ = sf.config(name, table)
+    for kv in filter(None, os.environ.get("OVERRIDE", "").split(",")):     # e.g. OVERRIDE=cie_cooling=1,three_body_rate=4
+        k, v = kv.split("=")
+        params[k] = int(v)
     pc = params["primordial_chemistry"]
     ch = capi.Chemistry(lib, **params).initialize()
     idx = torch.arange(n, dtype=torch.int64, device=dev)
