@@ -378,7 +378,9 @@ __device__ inline double dust_temperature(const GrParams &P, double tgas, double
     td = td - ddiv_s(sol, slope);
     pert = dmax(dmin(pert, ddiv_s(0.5 * fabs(td - told), td)), 1.e-10);
     if (td < trad) newton = false;                       // give up, bisection takes over
-    else if (fabs(ddiv_s(sol, solp)) < 1.e-5) { newton = false; bisect = false; }
+    // |sol / solp| < 1e-5 as a product: the quotient is only compared, never used (the two forms can differ
+    // only when the quotient is within an ulp of the threshold)
+    else if (fabs(sol) < 1.e-5 * fabs(solp)) { newton = false; bisect = false; }
   }
   if (bisect) {
     td = trad;
@@ -388,7 +390,7 @@ __device__ inline double dust_temperature(const GrParams &P, double tgas, double
       if (it == 1) mid = dmin(mid, t_subl);
       const double sol = gr_balance(mid, tgas, kappa_gr(mid), trad4, gasgr, gamma_isrf, nh);
       if (sol > 0.0) td = mid; else hi = mid;
-      if (ddiv_s(fabs(hi - td), td) <= 1.e-3) break;
+      if (fabs(hi - td) <= 1.e-3 * td) break;          // (td >= trad >= 1: the division of the reference as a product)
     }
   }
   return td;
