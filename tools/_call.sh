@@ -1,5 +1,5 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
-CONFIGS=C3 python tools/bench_configs.py 23 B 2>&1 | grep -E "Mcell|rror"
-CONFIGS=HARNESS python tools/bench_configs.py 21 H 2>&1 | grep -E "Mcell|rror"
-python -m pytest tests/test_gpu_parity.py tests/test_gpu_variants.py tests/test_gpu_parity_large.py -m gpu -x -q 2>&1 | tail -3
+( time timeout 1800 python -m pytest tests -m gpu -x -q -rs ) > gpurun_out/r2h_pytest.log 2>&1; grep -E "passed|failed|FAILED" gpurun_out/r2h_pytest.log
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1 | cut -c1-250
+( time python bench.py > gpurun_out/r2h_bench_n1.json 2> gpurun_out/r2h_bench_n1.err ); tail -2 gpurun_out/r2h_bench_n1.err | cut -c1-300
